@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: fused RK-stage kernels for 3-D Burgers (WENO5) and 3-D heat.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one time step = 3 fused RK stages over the whole field (one pass of the hot path).
+Default workload `burgers3d_weak512`: BASELINE.json config 5's weak-scaling case, 512x512x(512*N)
+double, WENO5-JS + SSP-RK3 with MultiGPU/Burgers3d_Baseline semantics, one z-slab of 512 planes
+per GPU (at N=1 simply 512^3).  Other workloads: burgers3d_256 (C3), heat3d_256 (C2),
+heat3d_strong1024 / burgers3d_strong1024 (C4/C5 strong scaling), heat2d_512 (C1).
+
+Prints ONE JSON line (rank 0).  value = cell-updates of all ranks / device time (max over ranks);
+e2e = same metric through the solver API with HOST buffers (upload + S steps + download);
+roofline = algorithmic HBM bytes of the stage kernel / its measured launch time vs the measured
+copy bandwidth; cpu_baseline = the CPU oracle (OpenMP port of the reference algorithm) on a
+bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (target, nx, ny, nz_per_gpu or total, scaling, lengths, coef, e2e steps)
+    "burgers3d_weak512": dict(target="burgers3d_mgpu", n=(512, 512, 512), scaling="weak", L=(2.0, 2.0, 2.0), coef=0.3, e2e_steps=20),
+    "burgers3d_256": dict(target="burgers3d_mgpu", n=(256, 256, 256), scaling="weak", L=(2.0, 2.0, 2.0), coef=0.3, e2e_steps=43),
+    "burgers3d_sgpu_256": dict(target="burgers3d_sgpu", n=(256, 256, 256), scaling="replicas", L=(2.0, 2.0, 2.0), coef=0.3, e2e_steps=43),
+    "burgers3d_strong1024": dict(target="burgers3d_mgpu", n=(1024, 1024, 1024), scaling="strong", L=(2.0, 2.0, 2.0), coef=0.3, e2e_steps=20),
+    "heat3d_256": dict(target="heat3d_mgpu", n=(256, 256, 256), scaling="weak", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=100),
+    "heat3d_weak512": dict(target="heat3d_mgpu", n=(512, 512, 512), scaling="weak", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
+    "heat3d_strong1024": dict(target="heat3d_mgpu", n=(1024, 1024, 1024), scaling="strong", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
+    "heat3d_sgpu_256": dict(target="heat3d_sgpu_baseline", n=(256, 256, 256), scaling="replicas", L=(10, 10, 10), coef=1.0, e2e_steps=100),
+}
+BYTES_PER_CELL_STEP = {8: 64.0, 4: 32.0}     # 16 + 24 + 24, per time step
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.stop_flag = threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def cpu_sample(w, precision_bytes, target_seconds=12.0):
+    """Times the CPU oracle (OpenMP, all host threads) on a bounded sample of the workload:
+    the full x-y extent and as many z planes as ~target_seconds of CPU work allow."""
+    from oracle import oracle as orc
+    import ctypes as C
+    nx, ny, _ = w["n"]
+    L = orc.lib()
+    dt_ = np.float64
+    threads = orc.num_threads()
+
+    def run(planes, steps):
+        if w["target"].startswith("burgers"):
+            u = orc.ic_burgers3d_mgpu(nx, ny, planes - 6)
+            uo, Lu = np.empty_like(u), np.empty_like(u)
+            dx = 2.0 / (nx - 1)
+            f = L.orc_burgers3d_mgpu_step_f64
+            f.argtypes = [C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_double] * 4
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                f(u.ctypes.data, uo.ctypes.data, Lu.ctypes.data, nx, ny, planes, dx, dx, dx, 0.3 * dx)
+            return time.perf_counter() - t0
+        u = orc.ic_heat3d_mgpu(nx, ny, planes - 6)
+        uo, Lu = np.empty_like(u), np.zeros_like(u)
+        f = L.orc_heat3d_step_f64
+        f.argtypes = [C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_double] * 4 + [C.c_int]
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            f(u.ctypes.data, uo.ctypes.data, Lu.ctypes.data, nx, ny, planes, 1.0, 1.0, 1.0, 1e-6, 2)
+        return time.perf_counter() - t0
+
+    planes = 14
+    t = run(planes, 1)                                  # calibration (also warms the pages)
+    rate = nx * ny * planes * 3 / t
+    planes = int(min(max(14, target_seconds * rate / (nx * ny * 3)), 262))
+    steps = 1
+    t = min(run(planes, steps) for _ in range(2))
+    cells = nx * ny * planes
+    return {"value": cells * 3 * steps / t / 1e6, "unit": "Mcell-updates/s", "cores": threads, "kind": "port",
+            "sample": "%dx%dx%d planes of the workload, %d time step (3 RK stages), oracle/advdiff_oracle.c with OpenMP, best of 2"
+                      % (nx, ny, planes, steps), "seconds": t}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="burgers3d_weak512", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    w = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    N = args.gpus
+    esz = 8 if args.precision == "f64" else 4
+    nx, ny, nz0 = w["n"]
+    nz_total = nz0 * N if w["scaling"] == "weak" else nz0
+    if w["scaling"] == "replicas":
+        nz_total = nz0
+    lz = w["L"][2] * (N if w["scaling"] == "weak" else 1)
+    config = {"workload": args.workload, "target": w["target"], "grid": [nx, ny, nz_total], "precision": args.precision,
+              "scheme": "WENO5-JS + Lax-Friedrichs + SSP-RK3" if "burgers" in w["target"] else "O4 13-pt Laplacian + SSP-RK3",
+              "decomposition": "z-slab x%d" % N if N > 1 else "single GPU",
+              "l2_policy": "no flush: working set 3 x %.2f GiB per GPU >> 126 MB L2" % (nx * ny * (nz_total / max(N, 1) + 6) * esz / 2**30)}
+
+    # ---------------------------------------------------------------- reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        vals = []
+        cb = None
+        for i in range(max(1, min(args.steps, 3))):
+            cb = cpu_sample(w, esz, target_seconds=8.0)
+            vals.append(cb["value"])
+        v = max(vals)
+        cb["value"] = v
+        line = {"impl": "reference", "metric": "Mcell-updates/s (3D %s, SSP-RK3)" % ("WENO5 Burgers" if "burgers" in w["target"] else "heat"),
+                "value": v, "unit": "Mcell-updates/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": 1e3 * cb["seconds"], "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
+                "dtype": args.precision, "data": "synthetic", "config": config, "cpu_baseline": cb,
+                "e2e": {"value": v, "unit": "Mcell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "reference arm = the reference algorithm on the host cores (no Matlab/Octave and no MPI on this "
+                        "image): OpenMP C port oracle/advdiff_oracle.c, pinned bit-exact to the reference's own kernels"}
+        print(json.dumps(line))
+        return 0
+
+    # ---------------------------------------------------------------- our arm (GPU)
+    import torch
+    import multigpu_advectiondiffusion_b200 as adv
+    import ctypes as C
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback exists)")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    assert world == N or world == 1, "launch with torchrun --nproc-per-node == --gpus"
+    dev = local_rank
+
+    comm_id = None
+    nranks = world if w["scaling"] != "replicas" else 1
+    if nranks > 1:
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            buf = (C.c_ubyte * 128)()
+            adv._lib.check(adv.lib().adv_comm_unique_id(C.byref(buf)))
+            idt.copy_(torch.tensor(list(buf), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        comm_id = bytes(idt.cpu().tolist())
+
+    s = adv.Solver(w["target"], nx, ny, nz_total, lx=w["L"][0], ly=w["L"][1], lz=lz, coef=w["coef"],
+                   precision=adv.F64 if esz == 8 else adv.F32, device=dev, nranks=nranks, rank=rank if nranks > 1 else 0,
+                   comm_id=comm_id)
+    s.init_reference_ic()
+    cells_local = nx * ny * (nz_total // nranks)
+    cells_job = cells_local * (world if w["scaling"] == "replicas" or nranks > 1 else 1)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    s.step(args.warmup)
+    s.sync()
+    sampler = ClockSampler(dev)
+    barrier()
+    sampler.start()
+    l0 = s.kernel_launches
+    t_wall0 = time.perf_counter()
+    s.step(args.steps)
+    s.sync()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = s.kernel_launches - l0
+    ms = s.elapsed_ms()
+    clocks = sampler.summary()
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = cells_job * 3 * args.steps / (ms * 1e-3) / 1e6
+
+    # roofline of the dominant kernel (the fused stage kernel; one launch per stage at N=1)
+    peak, peak_src = measured_peak()
+    per_launch_bytes = BYTES_PER_CELL_STEP[esz] / 3.0 * cells_local
+    launch_s = ms * 1e-3 / (3 * args.steps)
+    achieved = per_launch_bytes / launch_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                "kernel": "burgers3d_stage" if "burgers" in w["target"] else "heat3d_stage",
+                "algorithmic_bytes_per_launch": per_launch_bytes,
+                "note": "FP64 WENO5 is bound by the FP64 pipe, not HBM (SURVEY F11); see DESIGN.md" if "burgers" in w["target"] and esz == 8 else ""}
+
+    # end to end through the solver API with host buffers: upload + S steps + download per e2e step
+    e2e = None
+    if not args.no_e2e:
+        S = w["e2e_steps"]
+        host = torch.empty(s.local_shape, dtype=torch.float64 if esz == 8 else torch.float32).pin_memory()
+        hnp = host.numpy()
+        s.download(hnp)
+        reps = max(1, min(3, args.steps))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            s.upload(hnp)
+            s.step(S)
+            s.download(hnp)
+        barrier()
+        te = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([te], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            te = float(t.item())
+        e2e = {"value": cells_job * 3 * S * reps / te / 1e6, "unit": "Mcell-updates/s",
+               "h2d_bytes_per_step": int(hnp.nbytes), "d2h_bytes_per_step": int(hnp.nbytes),
+               "definition": "one e2e step = adv_upload(pinned host slab) + %d time steps + adv_download, as one run of the reference driver" % S,
+               "steps_per_call": S, "calls": reps}
+
+    cb = None
+    if rank == 0 and N == 1 and not args.no_cpu_baseline:
+        cb = cpu_sample(w, esz)
+
+    s.close()
+    if rank == 0:
+        line = {"metric": "Mcell-updates/s (3D %s, SSP-RK3, %s)" % ("WENO5 Burgers" if "burgers" in w["target"] else "heat", args.precision),
+                "value": value, "unit": "Mcell-updates/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
+                "dtype": args.precision, "data": "synthetic", "config": config,
+                "hbm_gbs": achieved * (world if nranks > 1 or w["scaling"] == "replicas" else 1),
+                "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks, "wall_s_timed_region": t_wall}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

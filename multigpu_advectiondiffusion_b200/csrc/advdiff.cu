@@ -1,0 +1,651 @@
+// libadvdiff.so -- C ABI (include/advdiff.h) over the fused sm_100a stage kernels.
+// Host side: plain C-callable functions, no torch, no CPU compute path: every entry point that
+// steps a field launches CUDA kernels and fails with ADV_ERR_NO_DEVICE / ADV_ERR_CUDA otherwise.
+#include "../../include/advdiff.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "burgers_kernels.cuh"
+#include "common.cuh"
+#include "halo.cuh"
+#include "heat_kernels.cuh"
+
+using namespace adv;
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return fail(_e == cudaErrorNoDevice || _e == cudaErrorInsufficientDriver           \
+                            ? ADV_ERR_NO_DEVICE : ADV_ERR_CUDA,                                \
+                        "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char* adv_last_error(void) { return g_err; }
+extern "C" int adv_version(void) { return ADV_VERSION; }
+
+extern "C" int adv_device_count(int* count)
+{
+    if (!count) return fail(ADV_ERR_INVALID, "count is NULL");
+    int n = 0, ok = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { *count = 0; return fail(ADV_ERR_NO_DEVICE, "cudaGetDeviceCount: %s", cudaGetErrorString(e)); }
+    for (int d = 0; d < n; d++) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major == 10) ok++;
+    }
+    *count = ok;
+    return ADV_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// stage launches
+// ------------------------------------------------------------------------------------------
+static bool is_heat(int t)
+{
+    return t == ADV_TARGET_HEAT2D_SGPU || t == ADV_TARGET_HEAT3D_SGPU_BASELINE ||
+           t == ADV_TARGET_HEAT3D_SGPU_BLOCKING || t == ADV_TARGET_HEAT3D_MGPU;
+}
+static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU; }
+
+static int check_stage_args(const adv_stage_args* a, const void* u_in, const void* uo, const void* u_out, int min_n)
+{
+    if (!a || !u_in || !u_out) return fail(ADV_ERR_INVALID, "NULL argument");
+    if (a->stage < 1 || a->stage > 3) return fail(ADV_ERR_INVALID, "stage must be 1, 2 or 3 (got %d)", a->stage);
+    if (a->stage > 1 && !uo) return fail(ADV_ERR_INVALID, "uo is required for stages 2 and 3");
+    if (u_out == u_in || (a->stage > 1 && u_out == uo)) return fail(ADV_ERR_INVALID, "u_out must not alias an input");
+    if (a->nx < min_n || a->ny < min_n) return fail(ADV_ERR_INVALID, "grid %dx%d smaller than the stencil needs (%d)", a->nx, a->ny, min_n);
+    if (a->pitch < (size_t)a->nx) return fail(ADV_ERR_INVALID, "pitch %zu < nx %d", a->pitch, a->nx);
+    return ADV_OK;
+}
+
+template <typename REAL>
+static int heat_args_from(const adv_stage_args* a, HeatArgs<REAL>& h)
+{
+    h.nx = a->nx; h.ny = a->ny; h.nzs = a->nzs;
+    h.pitch = (long long)a->pitch; h.plane = (long long)a->pitch * a->ny;
+    h.kb = a->k_begin; h.ke = a->k_end;
+    h.stage = a->stage;
+    h.kx = (REAL)a->kx; h.ky = (REAL)a->ky; h.kz = (REAL)a->kz; h.dt = (REAL)a->dt;
+    h.iso = 0;
+    const int nx = a->nx, ny = a->ny, nz = a->nzs;
+    switch (a->target) {
+    case ADV_TARGET_HEAT2D_SGPU:            // kernels.cu:53,83
+        h.lap = Box3{{3, 3, 0}, {nx - 4, ny - 4, 0}};
+        h.rk = h.lap;
+        break;
+    case ADV_TARGET_HEAT3D_SGPU_BASELINE:   // kernels.cu:94,127
+        h.lap = Box3{{2, 2, 2}, {nx - 3, ny - 3, nz - 3}};
+        h.rk = h.lap;
+        break;
+    case ADV_TARGET_HEAT3D_SGPU_BLOCKING:   // kernels.cu:59-85 (3, nz-2, 16) ; :113
+        h.lap = Box3{{3, 3, 3}, {nx - 4, ny - 4, nz - 3}};
+        h.rk = Box3{{2, 2, 2}, {nx - 3, ny - 3, nz - 3}};
+        break;
+    case ADV_TARGET_HEAT3D_MGPU:            // Kernels.cu:236,288
+        h.lap = Box3{{3, 3, a->own_lo}, {nx - 4, ny - 4, a->own_hi - 1}};
+        h.rk = Box3{{3, 3, 0}, {nx - 4, ny - 4, nz - 1}};
+        h.iso = 1;
+        break;
+    default:
+        return fail(ADV_ERR_INVALID, "target %d is not a heat target", a->target);
+    }
+    return ADV_OK;
+}
+
+template <typename REAL>
+static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+{
+    int rc = check_stage_args(a, u_in, uo, u_out, 5);
+    if (rc) return rc;
+    if (a->k_begin < 0 || a->k_end > a->nzs || a->k_begin > a->k_end) return fail(ADV_ERR_INVALID, "bad plane window [%d,%d) of %d", a->k_begin, a->k_end, a->nzs);
+    if (a->k_begin == a->k_end) return ADV_OK;
+    HeatArgs<REAL> h;
+    rc = heat_args_from<REAL>(a, h);
+    if (rc) return rc;
+    constexpr int CHUNK = 32;
+    dim3 block(32, 8, 1);
+    dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
+    heat3d_stage_direct<REAL, CHUNK><<<grid, block, 0, st>>>(h, u_in, a->stage == 1 ? u_in : uo, u_out);
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
+template <typename REAL>
+static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+{
+    int rc = check_stage_args(a, u_in, uo, u_out, 7);
+    if (rc) return rc;
+    HeatArgs<REAL> h;
+    adv_stage_args b = *a;
+    b.nzs = 1; b.k_begin = 0; b.k_end = 1;
+    rc = heat_args_from<REAL>(&b, h);
+    if (rc) return rc;
+    dim3 block(32, 8, 1);
+    dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, 1);
+    heat2d_stage_direct<REAL><<<grid, block, 0, st>>>(h, u_in, a->stage == 1 ? u_in : uo, u_out);
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
+template <typename REAL>
+static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, REAL* rowacc, cudaStream_t st)
+{
+    int rc = check_stage_args(a, u_in, uo, u_out, 7);
+    if (rc) return rc;
+    if (a->k_begin < 0 || a->k_end > a->nzs || a->k_begin > a->k_end) return fail(ADV_ERR_INVALID, "bad plane window [%d,%d) of %d", a->k_begin, a->k_end, a->nzs);
+    if (a->own_lo < 3 || a->own_hi > a->nzs - 3) return fail(ADV_ERR_INVALID, "owned planes [%d,%d) need 3 planes of halo inside [0,%d)", a->own_lo, a->own_hi, a->nzs);
+    if (a->k_begin == a->k_end) return ADV_OK;
+    const bool mg = a->target == ADV_TARGET_BURGERS3D_MGPU;
+    if (!mg && a->target != ADV_TARGET_BURGERS3D_SGPU) return fail(ADV_ERR_INVALID, "target %d is not a Burgers target", a->target);
+    if (mg && !rowacc) return fail(ADV_ERR_INVALID, "rowacc scratch is required for ADV_TARGET_BURGERS3D_MGPU");
+
+    BurgersArgs<REAL> b;
+    b.nx = a->nx; b.ny = a->ny; b.nzs = a->nzs;
+    b.pitch = (long long)a->pitch; b.plane = (long long)a->pitch * a->ny;
+    b.kb = a->k_begin; b.ke = a->k_end; b.own_lo = a->own_lo; b.own_hi = a->own_hi;
+    b.stage = a->stage;
+    b.dt = (REAL)a->dt; b.dx = (REAL)a->dx; b.dy = (REAL)a->dy; b.dz = (REAL)a->dz;
+    b.rdx = REAL(1) / b.dx; b.rdy = REAL(1) / b.dy; b.rdz = REAL(1) / b.dz;
+    b.kx = (REAL)a->kx; b.ky = (REAL)a->ky; b.kz = (REAL)a->kz;
+    b.visc = (!mg && (a->kx != 0 || a->ky != 0 || a->kz != 0)) ? 1 : 0;
+    b.quirk_lo = 1; b.quirk_hi = 0;
+    if (!mg && !(a->flags & ADV_FLAG_VISC_ONCE)) { b.quirk_lo = 16 - a->k_global0; b.quirk_hi = 18 - a->k_global0; }
+
+    constexpr int CHUNK = 16;
+    dim3 block(32, 4, 1);
+    dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
+    if (mg)
+        burgers3d_stage_direct<REAL, WENO_JS, BMODE_MGPU, CHUNK><<<grid, block, 0, st>>>(b, u_in, a->stage == 1 ? u_in : uo, u_out, rowacc);
+    else
+        burgers3d_stage_direct<REAL, WENO_Z, BMODE_SGPU, CHUNK><<<grid, block, 0, st>>>(b, u_in, a->stage == 1 ? u_in : uo, u_out, rowacc);
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
+extern "C" int adv_heat3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* st)
+{ return heat3d_stage_impl<double>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_heat3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* st)
+{ return heat3d_stage_impl<float>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_heat2d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* st)
+{ return heat2d_stage_impl<double>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_heat2d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* st)
+{ return heat2d_stage_impl<float>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_burgers3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, double* rowacc, void* st)
+{ return burgers3d_stage_impl<double>(a, u_in, uo, u_out, rowacc, (cudaStream_t)st); }
+extern "C" int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, float* rowacc, void* st)
+{ return burgers3d_stage_impl<float>(a, u_in, uo, u_out, rowacc, (cudaStream_t)st); }
+
+// ------------------------------------------------------------------------------------------
+// solver handle
+// ------------------------------------------------------------------------------------------
+struct adv_solver {
+    adv_desc d;
+    size_t esz;                 // sizeof(REAL)
+    int nzl;                    // physical planes owned by this rank
+    int nzs;                    // stored planes (nzl + 6 for MGPU targets)
+    size_t pitch;               // elements
+    size_t buf_bytes;
+    void* buf[3];               // ping-pong field buffers; buf[cur] holds the solution
+    int cur;
+    void* rowacc;               // Burgers MGPU scratch (pitch * nzs)
+    cudaStream_t stream, comm_stream;
+    cudaEvent_t ev_start, ev_stop, ev_boundary, ev_comm;
+    bool uploaded;
+    long long launches;
+    // constants in double (computed in REAL then widened, see make_constants)
+    double dx, dy, dz, dt_fixed, kx, ky, kz, visc_c;
+    HaloComm comm;
+};
+
+// The drivers compute their constants in REAL; keep that arithmetic (a5 in SURVEY.md 8a).
+template <typename REAL>
+static void make_constants(adv_solver* s)
+{
+    const adv_desc& d = s->d;
+    const REAL L = (REAL)d.lx, W = (REAL)d.ly, H = (REAL)d.lz;
+    const unsigned Nx = d.nx, Ny = d.ny, Nz = d.nz;
+    REAL dx = L / (Nx - 1), dy = W / (Ny - 1), dz = 0;
+    REAL dt = 0, kx = 0, ky = 0, kz = 0, C = 0;
+    switch (d.target) {
+    case ADV_TARGET_HEAT2D_SGPU: {          // SingleGPU/Diffusion2d/main.cpp:53-58
+        C = (REAL)d.coef;
+        dt = 1 / (2 * C * (1 / dx / dx + 1 / dy / dy)) * 0.9;
+        kx = C / (12 * dx * dx); ky = C / (12 * dy * dy);
+        break;
+    }
+    case ADV_TARGET_HEAT3D_SGPU_BASELINE:
+    case ADV_TARGET_HEAT3D_SGPU_BLOCKING: { // SingleGPU/Diffusion3d_baselineCode/main.cpp:55-61
+        C = (REAL)d.coef;
+        dz = H / (Nz - 1);
+        dt = 1 / (2 * C * (1 / dx / dx + 1 / dy / dy + 1 / dz / dz)) * 0.9;
+        kx = C / (12 * dx * dx); ky = C / (12 * dy * dy); kz = C / (12 * dz * dz);
+        break;
+    }
+    case ADV_TARGET_HEAT3D_MGPU: {          // MultiGPU/Diffusion3d_Baseline/main.c:61-67
+        C = (REAL)d.coef;
+        dz = H / (Nz - 1);
+        dt = 1 / (2 * C * (1 / dx / dx + 1 / dy / dy + 1 / dz / dz)) * 0.8;
+        kx = C / (12 * dx * dx); ky = C / (12 * dy * dy); kz = C / (12 * dz * dz);
+        break;
+    }
+    case ADV_TARGET_BURGERS3D_SGPU: {       // SingleGPU/Burgers3d_WENO5/main.cpp:53-59,130-132
+        dz = H / (Nz - 1);
+        C = 0.00001;
+        kx = C / (12 * dx * dx); ky = C / (12 * dy * dy); kz = C / (12 * dz * dz);
+        REAL dt1 = (REAL)d.coef * dx / 1.0;
+        REAL dt2 = 1. / (2 * C * (1 / dx / dx + 1 / dy / dy + 1 / dz / dz)) * 0.9;
+        dt = dt1 < dt2 ? dt1 : dt2;
+        break;
+    }
+    case ADV_TARGET_BURGERS3D_MGPU: {       // MultiGPU/Burgers3d_Baseline/main.c:61-63,193
+        dz = H / (Nz - 1);
+        dt = (REAL)d.coef * dx / 1.0;
+        break;
+    }
+    }
+    s->dx = dx; s->dy = dy; s->dz = dz; s->dt_fixed = dt; s->kx = kx; s->ky = ky; s->kz = kz; s->visc_c = C;
+}
+
+static int validate_desc(const adv_desc* d)
+{
+    if (!d) return fail(ADV_ERR_INVALID, "desc is NULL");
+    if (d->target < ADV_TARGET_HEAT2D_SGPU || d->target > ADV_TARGET_BURGERS3D_MGPU) return fail(ADV_ERR_INVALID, "unknown target %d", d->target);
+    if (d->precision != ADV_F64 && d->precision != ADV_F32) return fail(ADV_ERR_INVALID, "unknown precision %d", d->precision);
+    const int minn = is_heat(d->target) ? 7 : 8;
+    if (d->nx < minn || d->ny < minn) return fail(ADV_ERR_INVALID, "grid too small: %d x %d", d->nx, d->ny);
+    if (d->target != ADV_TARGET_HEAT2D_SGPU && d->nz < minn) return fail(ADV_ERR_INVALID, "grid too small: nz=%d", d->nz);
+    const int P = d->nranks <= 0 ? 1 : d->nranks;
+    if (P > 1 && !is_mgpu(d->target)) return fail(ADV_ERR_INVALID, "z-slab decomposition needs an MGPU target");
+    if (P > 1) {
+        if (d->rank < 0 || d->rank >= P) return fail(ADV_ERR_INVALID, "rank %d outside [0,%d)", d->rank, P);
+        // the reference silently drops planes when Nz %% P != 0 (main.c:64); refuse instead
+        if (d->nz % P) return fail(ADV_ERR_INVALID, "nz=%d is not divisible by nranks=%d", d->nz, P);
+        if (d->nz / P < 2 * ADV_RADIUS) return fail(ADV_ERR_INVALID, "slab of %d planes is thinner than 2*RADIUS", d->nz / P);
+    }
+    if (!(d->coef > 0)) return fail(ADV_ERR_INVALID, "coef (C/K/CFL) must be positive");
+    return ADV_OK;
+}
+
+extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
+{
+    if (!out) return fail(ADV_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int rc = validate_desc(desc);
+    if (rc) return rc;
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (ndev == 0) return fail(ADV_ERR_NO_DEVICE, "no CUDA device");
+    if (desc->device < 0 || desc->device >= ndev) return fail(ADV_ERR_INVALID, "device %d outside [0,%d)", desc->device, ndev);
+    int major = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, desc->device));
+    if (major != 10) return fail(ADV_ERR_NO_DEVICE, "device %d is sm_%d0; this library is built for sm_100a only", desc->device, major);
+    CUDA_TRY(cudaSetDevice(desc->device));
+
+    adv_solver* s = new (std::nothrow) adv_solver();
+    if (!s) return fail(ADV_ERR_NOMEM, "out of host memory");
+    memset((void*)s, 0, sizeof(*s));
+    s->d = *desc;
+    if (s->d.nranks <= 0) { s->d.nranks = 1; s->d.rank = 0; }
+    if (s->d.target == ADV_TARGET_HEAT2D_SGPU) s->d.nz = 1;
+    s->esz = desc->precision == ADV_F64 ? 8 : 4;
+    s->nzl = s->d.nz / s->d.nranks;
+    s->nzs = is_mgpu(desc->target) ? s->nzl + 2 * ADV_RADIUS : s->nzl;
+    const size_t align = 128 / s->esz;                  // rows start on 128-byte lines
+    s->pitch = ((size_t)desc->nx + align - 1) / align * align;
+    s->buf_bytes = s->pitch * (size_t)desc->ny * (size_t)s->nzs * s->esz;
+    if (desc->precision == ADV_F64) make_constants<double>(s); else make_constants<float>(s);
+
+#define CREATE_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { \
+        int _c = fail(_e == cudaErrorMemoryAllocation ? ADV_ERR_NOMEM : ADV_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e)); \
+        adv_destroy(s); return _c; } } while (0)
+    for (int b = 0; b < 3; b++) CREATE_TRY(cudaMalloc(&s->buf[b], s->buf_bytes));
+    if (desc->target == ADV_TARGET_BURGERS3D_MGPU) {
+        CREATE_TRY(cudaMalloc(&s->rowacc, s->pitch * (size_t)s->nzs * s->esz));
+        CREATE_TRY(cudaMemset(s->rowacc, 0, s->pitch * (size_t)s->nzs * s->esz));
+    }
+    CREATE_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
+    CREATE_TRY(cudaEventCreate(&s->ev_start));
+    CREATE_TRY(cudaEventCreate(&s->ev_stop));
+    CREATE_TRY(cudaEventCreateWithFlags(&s->ev_boundary, cudaEventDisableTiming));
+    CREATE_TRY(cudaEventCreateWithFlags(&s->ev_comm, cudaEventDisableTiming));
+#undef CREATE_TRY
+    if (s->d.nranks > 1) {
+        rc = s->comm.init(s->d.nranks, s->d.rank, s->d.comm_id, g_err, sizeof(g_err));
+        if (rc) { adv_destroy(s); return rc; }
+    }
+    *out = s;
+    return ADV_OK;
+}
+
+extern "C" int adv_destroy(adv_solver* s)
+{
+    if (!s) return ADV_OK;
+    cudaSetDevice(s->d.device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
+    s->comm.destroy();
+    for (int b = 0; b < 3; b++) if (s->buf[b]) cudaFree(s->buf[b]);
+    if (s->rowacc) cudaFree(s->rowacc);
+    if (s->ev_start) cudaEventDestroy(s->ev_start);
+    if (s->ev_stop) cudaEventDestroy(s->ev_stop);
+    if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);
+    if (s->ev_comm) cudaEventDestroy(s->ev_comm);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    if (s->comm_stream) cudaStreamDestroy(s->comm_stream);
+    delete s;
+    return ADV_OK;
+}
+
+extern "C" size_t adv_local_elems(const adv_solver* s) { return s ? (size_t)s->d.nx * s->d.ny * s->nzs : 0; }
+extern "C" double adv_dt(const adv_solver* s) { return s ? s->dt_fixed : 0.0; }
+extern "C" long long adv_kernel_launches(const adv_solver* s) { return s ? s->launches : 0; }
+
+extern "C" int adv_upload(adv_solver* s, const void* host)
+{
+    if (!s || !host) return fail(ADV_ERR_INVALID, "NULL argument");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    const size_t row = (size_t)s->d.nx * s->esz;
+    CUDA_TRY(cudaMemcpy2DAsync(s->buf[s->cur], s->pitch * s->esz, host, row, row, (size_t)s->d.ny * s->nzs,
+                               cudaMemcpyHostToDevice, s->stream));
+    s->uploaded = true;
+    return ADV_OK;
+}
+
+extern "C" int adv_download(adv_solver* s, void* host)
+{
+    if (!s || !host) return fail(ADV_ERR_INVALID, "NULL argument");
+    if (!s->uploaded) return fail(ADV_ERR_STATE, "no field uploaded yet");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    const size_t row = (size_t)s->d.nx * s->esz;
+    CUDA_TRY(cudaMemcpy2DAsync(host, row, s->buf[s->cur], s->pitch * s->esz, row, (size_t)s->d.ny * s->nzs,
+                               cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return ADV_OK;
+}
+
+extern "C" int adv_device_field(adv_solver* s, void** dptr, size_t* pitch)
+{
+    if (!s || !dptr) return fail(ADV_ERR_INVALID, "NULL argument");
+    *dptr = s->buf[s->cur];
+    if (pitch) *pitch = s->pitch;
+    return ADV_OK;
+}
+
+extern "C" int adv_sync(adv_solver* s)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    CUDA_TRY(cudaStreamSynchronize(s->comm_stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return ADV_OK;
+}
+
+extern "C" int adv_last_elapsed_ms(adv_solver* s, float* ms)
+{
+    if (!s || !ms) return fail(ADV_ERR_INVALID, "NULL argument");
+    CUDA_TRY(cudaEventSynchronize(s->ev_stop));
+    CUDA_TRY(cudaEventElapsedTime(ms, s->ev_start, s->ev_stop));
+    return ADV_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// reference initial conditions, generated on the host with libm exactly as the reference does
+// ------------------------------------------------------------------------------------------
+template <typename REAL>
+static void reference_ic_local(const adv_solver* s, REAL* h)
+{
+    const adv_desc& d = s->d;
+    const int nx = d.nx, ny = d.ny;
+    const REAL dx = (REAL)s->dx, dy = (REAL)s->dy, dz = (REAL)s->dz;
+    const int NZ = is_mgpu(d.target) ? d.nz + 2 * ADV_RADIUS : d.nz;     // global stored planes
+    const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;            // Init_subdomain, Tools.c:181-200
+    for (int kl = 0; kl < s->nzs; kl++) {
+        const int k = kl + kg0;
+        for (int j = 0; j < ny; j++)
+            for (int i = 0; i < nx; i++) {
+                const size_t o = (size_t)i + (size_t)nx * j + (size_t)nx * ny * kl;
+                REAL v = 0;
+                switch (d.target) {
+                case ADV_TARGET_HEAT2D_SGPU:        // SingleGPU/Diffusion2d/tools.cpp:109-118
+                    v = exp(-((-5 + i * dx) * (-5 + i * dx) + (-5 + j * dy) * (-5 + j * dy)) / (4 * 1.0 * 0.1));
+                    if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1) v = 0.0;
+                    break;
+                case ADV_TARGET_HEAT3D_SGPU_BASELINE:
+                case ADV_TARGET_HEAT3D_SGPU_BLOCKING: // SingleGPU/Diffusion3d_baselineCode/tools.cpp:128-139
+                    v = exp(-((-5 + i * dx) * (-5 + i * dx) + (-5 + j * dy) * (-5 + j * dy) + (-5 + k * dz) * (-5 + k * dz)) / (4 * 1.0 * 0.1));
+                    if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1 || k == 0 || k == NZ - 1) v = 0.0;
+                    break;
+                case ADV_TARGET_HEAT3D_MGPU:        // MultiGPU/Diffusion3d_Baseline/Tools.c:129-143 (case 1)
+                    v = (i >= nx / 4 && i < 3 * nx / 4 && j >= ny / 4 && j < 3 * ny / 4 && k >= NZ / 4 && k < 3 * NZ / 4) ? 1. : 0.;
+                    break;
+                case ADV_TARGET_BURGERS3D_SGPU: {   // SingleGPU/Burgers3d_WENO5/tools.cpp:126-136
+                    const REAL x = i * dx, y = j * dy, z = k * dz;
+                    v = 1.0 * exp(-((x - 1.0) * (x - 1.0) + (y - 1.0) * (y - 1.0) + (z - 1.0) * (z - 1.0)) / 0.1);
+                    break;
+                }
+                case ADV_TARGET_BURGERS3D_MGPU:     // MultiGPU/Burgers3d_Baseline/Tools.c:158-173 (macro pastes
+                                                    // unparenthesised arguments: ((a*d)*a)*d)
+                    if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1 || k == 0 || k == NZ - 1) v = 0.0;
+                    else v = 1.0 * exp(-(((0.5 * (nx - 1) - i) * dx * (0.5 * (nx - 1) - i) * dx) +
+                                          ((0.5 * (ny - 1) - j) * dy * (0.5 * (ny - 1) - j) * dy) +
+                                          ((0.5 * (NZ - 1) - k) * dz * (0.5 * (NZ - 1) - k) * dz)) / 0.1);
+                    break;
+                }
+                h[o] = v;
+            }
+    }
+}
+
+extern "C" int adv_init_reference_ic(adv_solver* s)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    const size_t n = adv_local_elems(s);
+    void* h = malloc(n * s->esz);
+    if (!h) return fail(ADV_ERR_NOMEM, "out of host memory");
+    if (s->esz == 8) reference_ic_local<double>(s, (double*)h); else reference_ic_local<float>(s, (float*)h);
+    int rc = adv_upload(s, h);
+    if (!rc) { cudaError_t e = cudaStreamSynchronize(s->stream); if (e != cudaSuccess) rc = fail(ADV_ERR_CUDA, "upload: %s", cudaGetErrorString(e)); }
+    free(h);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// one time step = three fused stages over ping-pong buffers A (u^n), B, C:
+//   B = S1(A);  C = S2(B; A);  B = S3(C; A);  then A <-> B.      (no uo copy, no Lu array)
+// With ranks > 1 each stage computes the two 3-plane boundary slabs first, hands them to the
+// halo exchange on the comm stream, and computes the interior while they travel.
+// ------------------------------------------------------------------------------------------
+static int launch_stage(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke, cudaStream_t st)
+{
+    if (kb >= ke) return ADV_OK;
+    adv_stage_args a;
+    memset(&a, 0, sizeof(a));
+    a.target = s->d.target; a.flags = s->d.flags; a.stage = stage;
+    a.nx = s->d.nx; a.ny = s->d.ny; a.nzs = s->nzs; a.pitch = s->pitch;
+    a.k_begin = kb; a.k_end = ke;
+    a.own_lo = is_mgpu(s->d.target) ? ADV_RADIUS : 3;
+    a.own_hi = s->nzs - 3;
+    a.k_global0 = 0;
+    a.dt = dt; a.dx = s->dx; a.dy = s->dy; a.dz = s->dz; a.kx = s->kx; a.ky = s->ky; a.kz = s->kz;
+    int rc;
+    const bool f64 = s->esz == 8;
+    switch (s->d.target) {
+    case ADV_TARGET_HEAT2D_SGPU:
+        rc = f64 ? adv_heat2d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, st)
+                 : adv_heat2d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, st);
+        break;
+    case ADV_TARGET_BURGERS3D_SGPU:
+    case ADV_TARGET_BURGERS3D_MGPU:
+        rc = f64 ? adv_burgers3d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, (double*)s->rowacc, st)
+                 : adv_burgers3d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, (float*)s->rowacc, st);
+        break;
+    default:
+        rc = f64 ? adv_heat3d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, st)
+                 : adv_heat3d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, st);
+    }
+    if (!rc) s->launches++;
+    return rc;
+}
+
+static int do_stage(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out)
+{
+    const int P = s->d.nranks, r = s->d.rank;
+    if (P == 1) return launch_stage(s, stage, dt, in, uo, out, 0, s->nzs, s->stream);
+
+    // planes this rank produces itself: owned [3, nzs-3) plus the global pad planes at the two ends
+    const int lo = (r == 0) ? 0 : ADV_RADIUS;
+    const int hi = (r == P - 1) ? s->nzs : s->nzs - ADV_RADIUS;
+    const int R = ADV_RADIUS;
+    int rc;
+    // the comm stream of the previous stage must be done with `in` ghosts before we read them
+    CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    // boundary slabs first: [3,6) goes to the left neighbour, [nzs-6,nzs-3) to the right one
+    if (r > 0)     { rc = launch_stage(s, stage, dt, in, uo, out, R, 2 * R, s->stream); if (rc) return rc; }
+    if (r < P - 1) { rc = launch_stage(s, stage, dt, in, uo, out, s->nzs - 2 * R, s->nzs - R, s->stream); if (rc) return rc; }
+    CUDA_TRY(cudaEventRecord(s->ev_boundary, s->stream));
+    CUDA_TRY(cudaStreamWaitEvent(s->comm_stream, s->ev_boundary, 0));
+    rc = s->comm.exchange(out, s->pitch * (size_t)s->d.ny, s->nzs, s->esz, s->comm_stream, g_err, sizeof(g_err));
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(s->ev_comm, s->comm_stream));
+    // interior (and the global-end pad planes) while the slabs travel
+    const int ilo = (r > 0) ? 2 * R : lo;
+    const int ihi = (r < P - 1) ? s->nzs - 2 * R : hi;
+    return launch_stage(s, stage, dt, in, uo, out, ilo, ihi, s->stream);
+}
+
+static int do_step(adv_solver* s, double dt)
+{
+    void* A = s->buf[s->cur];
+    void* B = s->buf[(s->cur + 1) % 3];
+    void* C = s->buf[(s->cur + 2) % 3];
+    int rc;
+    if ((rc = do_stage(s, 1, dt, A, A, B))) return rc;
+    if ((rc = do_stage(s, 2, dt, B, A, C))) return rc;
+    if ((rc = do_stage(s, 3, dt, C, A, B))) return rc;
+    s->cur = (s->cur + 1) % 3;
+    return ADV_OK;
+}
+
+extern "C" int adv_step(adv_solver* s, int nsteps)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_step before adv_upload");
+    if (nsteps < 0) return fail(ADV_ERR_INVALID, "nsteps < 0");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    CUDA_TRY(cudaEventRecord(s->ev_start, s->stream));
+    for (int n = 0; n < nsteps; n++) {
+        int rc = do_step(s, s->dt_fixed);
+        if (rc) return rc;
+    }
+    if (s->d.nranks > 1) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
+    return ADV_OK;
+}
+
+template <typename REAL>
+static int run_until_impl(adv_solver* s, double tEnd_d, int max_steps, double* dt_last, double* steps, double* t_reached)
+{
+    // main.c:190-196 / main.cpp:127-136: REAL t, it, dt; fixed dt, clipped on the last step (Burgers).
+    // MultiGPU heat (main.c:189-193) does not clip.
+    const bool clip = !is_heat(s->d.target);
+    const REAL tEnd = (REAL)tEnd_d;
+    REAL dt = 0, it = 0, t = 0;
+    while (t < tEnd && (max_steps < 0 || it < max_steps)) {
+        dt = (REAL)s->dt_fixed;
+        if (clip && (t + dt) > tEnd) { dt = tEnd - t; }
+        t += dt; it += 1;
+        int rc = do_step(s, (double)dt);
+        if (rc) return rc;
+    }
+    if (dt_last) *dt_last = dt;
+    if (steps) *steps = it;
+    if (t_reached) *t_reached = t;
+    return ADV_OK;
+}
+
+extern "C" int adv_run_until(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_run_until before adv_upload");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    CUDA_TRY(cudaEventRecord(s->ev_start, s->stream));
+    int rc = s->esz == 8 ? run_until_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
+                         : run_until_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
+    if (rc) return rc;
+    if (s->d.nranks > 1) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
+    return ADV_OK;
+}
+
+extern "C" int adv_solve_host(const adv_desc* desc, const void* host_in, void* host_out,
+                              double tEnd_or_iters, double* dt_last, double* steps, double* t_reached)
+{
+    if (!desc || !host_in || !host_out) return fail(ADV_ERR_INVALID, "NULL argument");
+    adv_desc d = *desc;
+    d.nranks = 1; d.rank = 0;
+    adv_solver* s = nullptr;
+    int rc = adv_create(&d, &s);
+    if (rc) return rc;
+    rc = adv_upload(s, host_in);
+    const bool iters_mode = is_heat(d.target) && d.target != ADV_TARGET_HEAT3D_MGPU;
+    if (!rc) {
+        if (iters_mode) {
+            rc = adv_step(s, (int)tEnd_or_iters);
+            if (dt_last) *dt_last = s->dt_fixed;
+            if (steps) *steps = (int)tEnd_or_iters;
+            if (t_reached) *t_reached = s->dt_fixed * (int)tEnd_or_iters;
+        } else {
+            rc = adv_run_until(s, tEnd_or_iters, -1, dt_last, steps, t_reached);
+        }
+    }
+    if (!rc) {
+        if (is_mgpu(d.target)) {
+            // Merge_domains (Tools.c:205-224): only owned planes are copied back; the six pad planes
+            // of the output keep the values of the input.
+            const size_t n = adv_local_elems(s), xy = (size_t)d.nx * d.ny;
+            void* tmp = malloc(n * s->esz);
+            if (!tmp) rc = fail(ADV_ERR_NOMEM, "out of host memory");
+            if (!rc) rc = adv_download(s, tmp);
+            if (!rc) {
+                if (host_out != host_in) memcpy(host_out, host_in, n * s->esz);
+                memcpy((char*)host_out + 3 * xy * s->esz, (char*)tmp + 3 * xy * s->esz, xy * (size_t)s->nzl * s->esz);
+            }
+            free(tmp);
+        } else {
+            rc = adv_download(s, host_out);
+        }
+    }
+    char keep[sizeof(g_err)];
+    memcpy(keep, g_err, sizeof(keep));
+    adv_destroy(s);
+    memcpy(g_err, keep, sizeof(keep));
+    return rc;
+}
+
+extern "C" int adv_comm_unique_id(unsigned char id[128])
+{
+    if (!id) return fail(ADV_ERR_INVALID, "id is NULL");
+    return HaloComm::unique_id(id, g_err, sizeof(g_err));
+}
