@@ -184,6 +184,24 @@ int adv_heat2d_stage_f32(const adv_stage_args* a, const float* u_in, const float
 int adv_burgers3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, double* rowacc, void* cuda_stream);
 int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, float* rowacc, void* cuda_stream);
 
+/* No counterpart in the reference.  adv_burgers3d_stage_f64 for ADV_TARGET_BURGERS3D_MGPU without the
+ * rowacc argument: the scratch is a fixed array inside the library's device image, so this entry point
+ * allocates nothing (no cudaMalloc/cudaFree, no allocating library call) -- for hosts that cannot allocate
+ * device memory where they call us: the device budget belongs to the embedding application's pool, the
+ * loop cannot take the device-wide synchronisation an allocation implies, or the caller has no allocator.
+ * Inputs and outputs are still the caller's buffers.
+ *  - Limit: pitch * nzs <= ADV_NOALLOC_MAX_ELEMS (9 MiB of doubles, enough for 1024 x (1024+6) planes);
+ *    larger fields are refused with ADV_ERR_INVALID and a message -- use the rowacc variant for them.
+ *  - Every GPU that loads the library carries those 9 MiB until the process exits.
+ *  - The first call on each device looks up the array's device address (with that device current, i.e.
+ *    the device the stream belongs to).  Make that first call before starting any stream capture.
+ *  - All calls on one device share the one array and it keeps what the last call left: stage 1 clears
+ *    the rows of the planes [k_begin,k_end) it produces, stages 2 and 3 continue from stage 1 of the same step.  Two time steps in flight on
+ *    the same GPU at once (different streams, or different fields interleaved stage by stage) race on it;
+ *    run them one after the other. */
+#define ADV_NOALLOC_MAX_ELEMS 1179648
+int adv_burgers3d_stage_f64_noalloc(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

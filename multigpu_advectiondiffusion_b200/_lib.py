@@ -17,6 +17,7 @@ TARGETS = {
 }
 F64, F32 = 0, 1
 FLAG_VISC_ONCE = 0x1
+NOALLOC_MAX_ELEMS = 1179648
 
 ERR_NAMES = {1: "INVALID", 2: "CUDA", 3: "NO_DEVICE", 4: "COMM", 5: "NOMEM", 6: "STATE"}
 
@@ -74,6 +75,7 @@ SIGNATURES = {
     "adv_heat2d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
     "adv_burgers3d_stage_f64": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P, _P]),
     "adv_burgers3d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P, _P]),
+    "adv_burgers3d_stage_f64_noalloc": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
 }
 
 _LIB = None

@@ -649,3 +649,66 @@ extern "C" int adv_comm_unique_id(unsigned char id[128])
     if (!id) return fail(ADV_ERR_INVALID, "id is NULL");
     return HaloComm::unique_id(id, g_err, sizeof(g_err));
 }
+
+// ------------------------------------------------------------------------------------------
+// Burgers stage without any allocation (adv_burgers3d_stage_f64_noalloc)
+//
+// Same kernel and same arithmetic as adv_burgers3d_stage_f64, but the j=2 row accumulator lives
+// in device memory that is part of this library's image instead of memory somebody allocated.
+// For hosts that may not allocate on the device at all: an embedding application that has
+// handed the whole device budget to its own pool, a time-critical loop that cannot afford the
+// device-wide synchronisation cudaMalloc/cudaFree imply, or a caller that simply owns no
+// allocator.  Nothing here calls cudaMalloc, cudaFree or any library routine that allocates.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_rowacc[ADV_NOALLOC_MAX_ELEMS];
+
+// In host code `g_noalloc_rowacc` is only a handle for the runtime, not an address the GPU can
+// use; the device address has to be asked for, once per device, with that device current.
+static double* noalloc_rowacc_for_current_device(int* rc_out)
+{
+    enum { MAX_DEV = 64 };
+    static double* ptr[MAX_DEV];            // zero-initialised; one slot per device ordinal
+    *rc_out = ADV_OK;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { *rc_out = fail(ADV_ERR_NO_DEVICE, "cudaGetDevice: %s", cudaGetErrorString(e)); return nullptr; }
+    if (dev < 0 || dev >= MAX_DEV) { *rc_out = fail(ADV_ERR_INVALID, "device ordinal %d not supported", dev); return nullptr; }
+    if (!ptr[dev]) {
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_rowacc);
+        if (e != cudaSuccess || !p) {
+            *rc_out = fail(ADV_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        ptr[dev] = p;
+    }
+    return ptr[dev];
+}
+
+extern "C" int adv_burgers3d_stage_f64_noalloc(const adv_stage_args* a, const double* u_in, const double* uo,
+                                               double* u_out, void* cuda_stream)
+{
+    if (!a) return fail(ADV_ERR_INVALID, "NULL argument");
+    if (a->target != ADV_TARGET_BURGERS3D_MGPU)
+        return fail(ADV_ERR_INVALID, "adv_burgers3d_stage_f64_noalloc serves ADV_TARGET_BURGERS3D_MGPU only (the other "
+                                     "targets use no scratch: call adv_burgers3d_stage_f64 with rowacc = NULL)");
+    if (a->nzs <= 0 || a->pitch == 0) return fail(ADV_ERR_INVALID, "empty field");
+    const unsigned long long need = (unsigned long long)a->pitch * (unsigned long long)a->nzs;
+    if (need > (unsigned long long)ADV_NOALLOC_MAX_ELEMS)
+        return fail(ADV_ERR_INVALID, "field needs %llu scratch elements (pitch %zu x %d planes) but the built-in scratch holds "
+                                     "%llu; use adv_burgers3d_stage_f64 with caller-provided scratch",
+                    need, a->pitch, a->nzs, (unsigned long long)ADV_NOALLOC_MAX_ELEMS);
+    int rc;
+    double* scratch = noalloc_rowacc_for_current_device(&rc);
+    if (!scratch) return rc;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (a->stage == 1 && a->k_begin >= 0 && a->k_end <= a->nzs && a->k_begin < a->k_end) {
+        // the accumulator of a new time step starts from zero (the reference zeroes Lu once per step,
+        // main.c:202); whatever an earlier call left in the shared array must not leak into this one.
+        // Only the rows of the planes this call produces are cleared, so a stage split into several
+        // plane windows does not wipe what an earlier window of the same stage wrote.
+        CUDA_TRY(cudaMemsetAsync(scratch + a->pitch * (size_t)a->k_begin, 0,
+                                 a->pitch * (size_t)(a->k_end - a->k_begin) * sizeof(double), st));
+    }
+    return burgers3d_stage_impl<double>(a, u_in, uo, u_out, scratch, st);
+}
