@@ -175,7 +175,25 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     constexpr int CHUNK = 16;
     dim3 block(32, 4, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
-    if (mg)
+    static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
+    if (mg && !force_direct) {
+        // tile variant: 0 = 32x8 tile, 2 CTAs/SM (default); 1 = 32x8, 1 CTA/SM, unconstrained registers; 2 = 32x16 tile
+        static const int variant = getenv("ADV_BURGERS_VARIANT") ? atoi(getenv("ADV_BURGERS_VARIANT")) : 0;
+        const int TY = variant == 2 ? 16 : 8;
+        const int planes = a->k_end - a->k_begin;
+        const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
+        // enough CTAs for ~4 waves of 2 CTAs/SM on 148 SMs, but chunks of at least 16 planes (6 planes of z run-in each)
+        int nch = (1184 + gx * gy - 1) / (gx * gy);
+        if (nch > planes / 16) nch = planes / 16;
+        if (nch < 1) nch = 1;
+        const int chunk = (planes + nch - 1) / nch;
+        dim3 tblock(32, TY + 1, 1);
+        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
+        const REAL* uo_ = a->stage == 1 ? u_in : uo;
+        if (variant == 2)      burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 16, 1><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+        else if (variant == 1) burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 8, 1><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+        else                   burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 8, 2><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+    } else if (mg)
         burgers3d_stage_direct<REAL, WENO_JS, BMODE_MGPU, CHUNK><<<grid, block, 0, st>>>(b, u_in, a->stage == 1 ? u_in : uo, u_out, rowacc);
     else
         burgers3d_stage_direct<REAL, WENO_Z, BMODE_SGPU, CHUNK><<<grid, block, 0, st>>>(b, u_in, a->stage == 1 ? u_in : uo, u_out, rowacc);

@@ -161,4 +161,270 @@ burgers3d_stage_direct(BurgersArgs<REAL> a, const REAL* __restrict__ u, const RE
     }
 }
 
+// =============================================================================================
+// v2 ("tiled"): every WENO reconstruction is evaluated exactly once.
+//
+// The face flux f_{c+1/2} = hn(c) + hp(c+1), where hn(c) (minus side, from f+ on c-2..c+2) and
+// hp(c) (plus side of face c-1/2, from f- on c-2..c+2) are both centred on cell c.  Each thread
+// therefore evaluates one (hn,hp) pair per direction for its own cell from ONE 5-point stencil of
+// (f+,f-) and obtains the neighbours' halves through warp shuffles (x), shared memory (y) or its
+// own register queue (z, one plane later).  By symmetry hp(a,b,c,d,e) == hn(e,d,c,b,a), so a single
+// routine serves both sides.  Per z-plane a CTA of TY compute warps (one row of 32 cells each)
+// + 1 "edge" warp (the 2*(32+TY) half reconstructions on the tile rim) works on a 32 x TY tile:
+//   - u of the tile + halo 3 is fetched one plane ahead into registers, converted once to
+//     (f+,f-) and parked in a double-buffered shared-memory slot (LDS.128 gets both);
+//   - z needs no shared memory: 5-deep (f+,f-) register queue, the cell is finished 3 planes
+//     behind the plane being staged.
+// Arithmetic: WENO weights through a common denominator (one division per side instead of the
+// reference's 7), divisions by dx,dy,dz,3 as multiplications by reciprocals, FMA contraction.
+// Same formulas, different rounding: parity is to 1e-12, not bitwise (tests/test_gpu_parity.py).
+// =============================================================================================
+template <typename REAL> struct V2T;
+template <> struct V2T<double> { typedef double2 type; };
+template <> struct V2T<float> { typedef float2 type; };
+
+__device__ __forceinline__ double fast_div(double num, double den)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(den));      // 2^-23 relative
+    double e = fma(-den, y, 1.0); y = fma(y, e, y);                // 2^-46
+    e = fma(-den, y, 1.0); y = fma(y, e, y);                       // ~2^-52
+    double q = num * y;
+    const double r = fma(-den, q, num);                            // one residual step
+    return fma(r, y, q);
+}
+__device__ __forceinline__ float fast_div(float num, float den) { return __fdividef(num, den); }
+
+// minus-side WENO5 value at the face right of cell c from (a,b,c,d,e) = f[c-2..c+2]
+template <typename REAL, int W>
+__device__ __forceinline__ REAL weno_side(REAL a, REAL b, REAL c, REAL d, REAL e)
+{
+    const REAL t0 = (a - 2 * b) + c, s0 = (a - 4 * b) + 3 * c;
+    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
+    const REAL t2 = (c - 2 * d) + e, s2 = (3 * c - 4 * d) + e;
+    // candidate values already divided by 6
+    const REAL q0 = REAL(2.0 / 6) * a - REAL(7.0 / 6) * b + REAL(11.0 / 6) * c;
+    const REAL q1 = REAL(-1.0 / 6) * b + REAL(5.0 / 6) * c + REAL(2.0 / 6) * d;
+    const REAL q2 = REAL(2.0 / 6) * c + REAL(5.0 / 6) * d - REAL(1.0 / 6) * e;
+    const REAL C1312 = REAL(13.0 / 12.0), C14 = REAL(0.25), EPS = REAL(1e-6);
+    if (W == WENO_JS) {
+        // P_k = (eps+B_k)^2 / d_k  =>  alpha_k = 1/P_k,  w_k = prod_{m!=k} P_m / sum
+        const REAL r0 = REAL(3.1622776601683795), r1 = REAL(1.2909944487358056), r2 = REAL(1.8257418583505538);  // 1/sqrt(.1,.6,.3)
+        REAL E0 = (r0 * C1312 * t0) * t0 + ((r0 * C14 * s0) * s0 + r0 * EPS);
+        REAL E1 = (r1 * C1312 * t1) * t1 + ((r1 * C14 * s1) * s1 + r1 * EPS);
+        REAL E2 = (r2 * C1312 * t2) * t2 + ((r2 * C14 * s2) * s2 + r2 * EPS);
+        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
+        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
+        const REAL den = (n0 + n1) + n2;
+        const REAL num = q0 * n0 + (q1 * n1 + q2 * n2);
+        return fast_div(num, den);
+    } else {
+        // alpha_k = d_k (e_k + tau)/e_k, e_k = B_k + eps;  multiply through by e0 e1 e2
+        const REAL e0 = (C1312 * t0) * t0 + ((C14 * s0) * s0 + EPS);
+        const REAL e1 = (C1312 * t1) * t1 + ((C14 * s1) * s1 + EPS);
+        const REAL e2 = (C1312 * t2) * t2 + ((C14 * s2) * s2 + EPS);
+        const REAL tau = fabs(e0 - e2);
+        const REAL A0 = (REAL(0.1) * (e0 + tau)) * (e1 * e2);
+        const REAL A1 = (REAL(0.6) * (e1 + tau)) * (e0 * e2);
+        const REAL A2 = (REAL(0.3) * (e2 + tau)) * (e0 * e1);
+        const REAL den = (A0 + A1) + A2;
+        const REAL num = q0 * A0 + (q1 * A1 + q2 * A2);
+        return fast_div(num, den);
+    }
+}
+
+template <typename REAL>
+__device__ __forceinline__ typename V2T<REAL>::type lf_split(REAL u)
+{
+    // f+ = 0.5*(0.5 u^2 + |u|u), f- = 0.5*(0.5 u^2 - |u|u): exactly 0.75/-0.25 times u^2 by sign
+    const REAL s = u * u;
+    typename V2T<REAL>::type r;
+    r.x = (u >= 0) ? REAL(0.75) * s : REAL(-0.25) * s;
+    r.y = (u >= 0) ? REAL(-0.25) * s : REAL(0.75) * s;
+    return r;
+}
+
+template <typename REAL, int TY>
+struct BurgersTileSmem {
+    static constexpr int TX = 32, H = 3;
+    static constexpr int RP = TX + 2 * H;              // slot row pitch (points)
+    static constexpr int ROWS = TY + 2 * H;
+    static constexpr int NPTS = RP * ROWS;
+    typename V2T<REAL>::type slot[2][NPTS];            // (f+, f-) of the staged plane
+    REAL exch_hn_y[TY][TX], exch_hp_y[TY][TX];
+    REAL edge_hn_x[TY], edge_hp_x[TY], edge_hn_y[TX], edge_hp_y[TX];
+};
+
+template <typename REAL, int W, int MODE, int TY, int MINB>
+__global__ void __launch_bounds__(32 * (TY + 1), MINB)
+burgers3d_stage_tiled(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
+                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
+{
+    typedef typename V2T<REAL>::type V2;
+    typedef BurgersTileSmem<REAL, TY> S;
+    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS;
+    constexpr int NT = 32 * (TY + 1);
+    constexpr int NPRE = (NPTS + NT - 1) / NT;
+    __shared__ __align__(16) S sm;
+
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int tid = ty * 32 + tx;
+    const bool edge_warp = (ty == TY);
+    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+    const int i = i0 + tx, j = j0 + ty;
+    const int kb = a.kb + blockIdx.z * chunk;
+    const int ke = min(kb + chunk, a.ke);
+    if (kb >= ke) return;
+    const long long P = a.pitch, Z = a.plane;
+    const bool in_dom = !edge_warp && i < a.nx && j < a.ny;
+    const long long col = (long long)i + P * j;
+
+    bool xact, yact, zact;
+    if (MODE == BMODE_MGPU) {
+        xact = (j >= 3 && j <= a.ny - 4) && (i >= 2 && i <= a.nx - 4);
+        yact = (i >= 3 && i <= a.nx - 4) && (j >= 2 && j <= a.ny - 4);
+        zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
+    } else {
+        xact = yact = zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
+    }
+
+    // tile point -> global offset for the cooperative plane fetch (constant over planes)
+    long long pre_off[NPRE];
+    bool pre_ok[NPRE];
+#pragma unroll
+    for (int n = 0; n < NPRE; n++) {
+        const int idx = tid + n * NT;
+        const int r = idx / RP, c = idx - r * RP;
+        const int gi = i0 - H + c, gj = j0 - H + r;
+        pre_ok[n] = idx < NPTS && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
+        pre_off[n] = (long long)gi + P * gj;
+    }
+    REAL pre[NPRE];
+    auto fetch = [&](int p) {
+        const bool pl = (p >= 0 && p < a.nzs);
+#pragma unroll
+        for (int n = 0; n < NPRE; n++) pre[n] = (pl && pre_ok[n]) ? u[pre_off[n] + Z * p] : REAL(0);
+    };
+    auto park = [&](int s) {
+#pragma unroll
+        for (int n = 0; n < NPRE; n++) {
+            const int idx = tid + n * NT;
+            if (idx < NPTS) sm.slot[s][idx] = lf_split<REAL>(pre[n]);
+        }
+    };
+
+    const int p_first = kb - 3, p_last = ke + 2;
+    fetch(p_first);
+    park(p_first & 1);
+    __syncthreads();
+
+    V2 z0, z1, z2, z3, z4;                      // (f+,f-) of planes p-4..p for this column
+    z0.x = z0.y = z1.x = z1.y = z2.x = z2.y = z3.x = z3.y = z4.x = z4.y = REAL(0);
+    REAL L1 = 0, L2 = 0, L3 = 0;                // Lxy of planes p-1, p-2, p-3
+    REAL hn_z_prev = 0, Fz_prev = 0;
+
+    for (int p = p_first; p <= p_last; p++) {
+        const int s = p & 1;
+        if (p < p_last) fetch(p + 1);           // next plane's u -> registers, consumed at the bottom
+        const V2* __restrict__ sl = sm.slot[s];
+        const bool xy_plane = (p >= kb && p < ke && p >= a.own_lo && p < a.own_hi);   // CTA-uniform
+        REAL hn_x = 0, hp_x = 0, hn_y = 0, hp_y = 0, hpR = 0, hnL = 0;
+        V2 c;
+        c.x = c.y = REAL(0);
+        if (!edge_warp) {
+            const int o = (ty + H) * RP + tx + H;
+            c = sl[o];
+            if (xy_plane) {
+                const V2 xm2 = sl[o - 2], xm1 = sl[o - 1], xp1 = sl[o + 1], xp2 = sl[o + 2];
+                hn_x = weno_side<REAL, W>(xm2.x, xm1.x, c.x, xp1.x, xp2.x);
+                hp_x = weno_side<REAL, W>(xp2.y, xp1.y, c.y, xm1.y, xm2.y);
+                const V2 ym2 = sl[o - 2 * RP], ym1 = sl[o - RP], yp1 = sl[o + RP], yp2 = sl[o + 2 * RP];
+                hn_y = weno_side<REAL, W>(ym2.x, ym1.x, c.x, yp1.x, yp2.x);
+                hp_y = weno_side<REAL, W>(yp2.y, yp1.y, c.y, ym1.y, ym2.y);
+                sm.exch_hn_y[ty][tx] = hn_y;
+                sm.exch_hp_y[ty][tx] = hp_y;
+                hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
+                hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
+            }
+        } else if (xy_plane) {
+            // rim of the tile: hn at column -1 / row -1, hp at column TX / row TY
+#pragma unroll
+            for (int it = tx; it < 2 * (TX + TY); it += 32) {
+                int oc, st;               // centre offset in the slot, stencil stride
+                bool minus;
+                if (it < TY)               { oc = (it + H) * RP + (H - 1);            st = 1;  minus = true;  }
+                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);      st = 1;  minus = false; }
+                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);   st = RP; minus = true;  }
+                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
+                const V2 m2 = sl[oc - 2 * st], m1 = sl[oc - st], cc = sl[oc], p1 = sl[oc + st], p2 = sl[oc + 2 * st];
+                // one evaluation for either side: hp(a,b,c,d,e) == hn(e,d,c,b,a)
+                const REAL v = weno_side<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
+                                                  minus ? p1.x : m1.y, minus ? p2.x : m2.y);
+                if (it < TY) sm.edge_hn_x[it] = v;
+                else if (it < 2 * TY) sm.edge_hp_x[it - TY] = v;
+                else if (it < 2 * TY + TX) sm.edge_hn_y[it - 2 * TY] = v;
+                else sm.edge_hp_y[it - 2 * TY - TX] = v;
+            }
+        }
+        __syncthreads();                        // exchange arrays complete
+
+        if (!edge_warp) {
+            REAL Lxy = REAL(0);
+            if (xy_plane) {
+                if (tx == 31) hpR = sm.edge_hp_x[ty];
+                if (tx == 0) hnL = sm.edge_hn_x[ty];
+                if (xact) {
+                    const REAL fu = hn_x + hpR;
+                    const REAL fu_old = (MODE == BMODE_MGPU && i == 2) ? REAL(0) : hnL + hp_x;
+                    Lxy = -(fu - fu_old) * a.rdx;
+                }
+                if (yact) {
+                    const REAL hnD = (ty == 0) ? sm.edge_hn_y[tx] : sm.exch_hn_y[ty - 1][tx];
+                    const REAL hpU = (ty == TY - 1) ? sm.edge_hp_y[tx] : sm.exch_hp_y[ty + 1][tx];
+                    const REAL gu = hn_y + hpU;
+                    const REAL gu_old = (MODE == BMODE_MGPU && j == 2) ? REAL(0) : hnD + hp_y;
+                    Lxy -= (gu - gu_old) * a.rdy;
+                }
+            }
+            // z: queue now holds planes p-4..p; pair centred on m = p-2 closes face m-1/2
+            z0 = z1; z1 = z2; z2 = z3; z3 = z4; z4 = c;
+            const int q = p - 3;                // the cell finished in this iteration
+            REAL Fz = 0, hn_z = 0;
+            if (p >= kb + 1) {                  // CTA-uniform
+                hn_z = weno_side<REAL, W>(z0.x, z1.x, z2.x, z3.x, z4.x);
+                const REAL hp_z = weno_side<REAL, W>(z4.y, z3.y, z2.y, z1.y, z0.y);
+                Fz = hn_z_prev + hp_z;
+            }
+            if (q >= kb && in_dom) {
+                const long long o = col + Z * q;
+                const REAL uq = u[o];
+                const bool owned = (q >= a.own_lo && q < a.own_hi);
+                const bool rk = (MODE == BMODE_MGPU) ? true : (owned && zact);
+                REAL res = uq;
+                if (rk) {
+                    REAL Lu = L3;
+                    if (owned) {
+                        if (MODE == BMODE_MGPU && j == 2 && yact) {
+                            const long long ra = (long long)i + P * q;
+                            if (a.stage > 1) Lu += rowacc[ra];
+                            rowacc[ra] = Lu;
+                        }
+                        if (zact) Lu -= (Fz - Fz_prev) * a.rdz;
+                    }
+                    const REAL qo = (a.stage == 1) ? uq : uo[o];
+                    const REAL t = uq + a.dt * Lu;
+                    res = (a.stage == 1) ? qo + a.dt * Lu
+                        : (a.stage == 2) ? REAL(0.75) * qo + REAL(0.25) * t
+                                         : (qo + REAL(2) * t) * REAL(1.0 / 3.0);
+                }
+                out[o] = res;
+            }
+            Fz_prev = Fz; hn_z_prev = hn_z;
+            L3 = L2; L2 = L1; L1 = Lxy;
+        }
+        if (p < p_last) park((p + 1) & 1);
+        __syncthreads();                        // next slot visible; exchange arrays free again
+    }
+}
+
 }  // namespace adv
