@@ -176,7 +176,32 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     dim3 block(32, 4, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
     static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
-    if (mg && !force_direct) {
+    fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
+    static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 1;
+    if (mg && !force_direct && ring > 0) {
+        // v3 ring kernel: 32x8 tile, 7-slot (f+,f-) plane ring in dynamic shared memory
+        constexpr int TY = 8;
+        typedef BurgersRingSmem<REAL, TY> RS;
+        const int planes = a->k_end - a->k_begin;
+        const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
+        int nch = (1776 + gx * gy - 1) / (gx * gy);        // ~4 waves of 3 CTAs/SM
+        if (nch > planes / 16) nch = planes / 16;
+        if (nch < 1) nch = 1;
+        const int chunk = (planes + nch - 1) / nch;
+        dim3 tblock(32, TY + 1, 1);
+        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
+        const REAL* uo_ = a->stage == 1 ? u_in : uo;
+        const size_t shm = sizeof(RS);
+        if (ring == 2) {
+            auto kfn = burgers3d_stage_ring<REAL, WENO_JS, BMODE_MGPU, TY, 2>;
+            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+            kfn<<<tgrid, tblock, shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+        } else {
+            auto kfn = burgers3d_stage_ring<REAL, WENO_JS, BMODE_MGPU, TY, 3>;
+            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
+            kfn<<<tgrid, tblock, shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+        }
+    } else if (mg && !force_direct) {
         // tile variant: 0 = 32x8 tile, 2 CTAs/SM (default); 1 = 32x8, 1 CTA/SM, unconstrained registers; 2 = 32x16 tile
         static const int variant = getenv("ADV_BURGERS_VARIANT") ? atoi(getenv("ADV_BURGERS_VARIANT")) : 0;
         const int TY = variant == 2 ? 16 : 8;

@@ -427,4 +427,230 @@ burgers3d_stage_tiled(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
     }
 }
 
+
+// =============================================================================================
+// v3 ("ring"): same algorithm as v2, restructured for the issue slot and the barrier.
+//  - the z stencil is read from a 7-slot shared-memory ring of (f+,f-) planes instead of per-thread
+//    register queues: the only loop-carried values are the lower z-face flux and two x partial sums;
+//  - the (hn,hp) halves of plane m+1 are produced in iteration m and consumed in iteration m+1, so
+//    one __syncthreads per plane is enough;
+//  - WENO constants come from the kernel-parameter constant bank, cell activity is predication.
+// Iteration m finishes plane m: planes m-2..m+3 live in the ring, plane m+4 is being staged.
+// =============================================================================================
+template <typename REAL, int W>
+__device__ __forceinline__ REAL weno_side_c(REAL a, REAL b, REAL c, REAL d, REAL e, const REAL* __restrict__ wc)
+{
+    const REAL t0 = (a - 2 * b) + c, s0 = (a - 4 * b) + 3 * c;
+    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
+    const REAL t2 = (c - 2 * d) + e, s2 = (3 * c - 4 * d) + e;
+    const REAL q0 = wc[9] * a - wc[10] * b + wc[11] * c;
+    const REAL q1 = wc[13] * c - wc[12] * b + wc[9] * d;
+    const REAL q2 = wc[9] * c + wc[13] * d - wc[12] * e;
+    const REAL E0 = (wc[0] * t0) * t0 + ((wc[3] * s0) * s0 + wc[6]);
+    const REAL E1 = (wc[1] * t1) * t1 + ((wc[4] * s1) * s1 + wc[7]);
+    const REAL E2 = (wc[2] * t2) * t2 + ((wc[5] * s2) * s2 + wc[8]);
+    if (W == WENO_JS) {
+        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
+        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
+        return fast_div(q0 * n0 + (q1 * n1 + q2 * n2), (n0 + n1) + n2);
+    } else {
+        const REAL tau = fabs(E0 - E2);
+        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
+        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
+        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
+        return fast_div(q0 * A0 + (q1 * A1 + q2 * A2), (A0 + A1) + A2);
+    }
+}
+
+template <typename REAL, int TY>
+struct BurgersRingSmem {
+    static constexpr int TX = 32, H = 3, NSLOT = 7;
+    static constexpr int RP = TX + 2 * H, ROWS = TY + 2 * H, NPTS = RP * ROWS;
+    typename V2T<REAL>::type slot[NSLOT][NPTS];
+    REAL hn_y[2][TY + 2][TX], hp_y[2][TY + 2][TX];     // row r+1 <-> tile row r; rows 0 / TY+1: rim
+    REAL edge_hn_x[2][TY], edge_hp_x[2][TY];
+};
+
+template <typename REAL, int W, int MODE, int TY, int MINB>
+__global__ void __launch_bounds__(32 * (TY + 1), MINB)
+burgers3d_stage_ring(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
+                     REAL* __restrict__ out, REAL* __restrict__ rowacc)
+{
+    typedef typename V2T<REAL>::type V2;
+    typedef BurgersRingSmem<REAL, TY> S;
+    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS, NSLOT = S::NSLOT;
+    constexpr int NT = 32 * (TY + 1);
+    constexpr int NPRE = (NPTS + NT - 1) / NT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    S& sm = *reinterpret_cast<S*>(smem_raw);
+
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int tid = ty * 32 + tx;
+    const bool edge_warp = (ty == TY);
+    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+    const int i = i0 + tx, j = j0 + ty;
+    const int kb = a.kb + blockIdx.z * chunk;
+    const int ke = min(kb + chunk, a.ke);
+    if (kb >= ke) return;
+    const long long P = a.pitch, Z = a.plane;
+    const bool in_dom = !edge_warp && i < a.nx && j < a.ny;
+    const long long col = (long long)i + P * j;
+    const REAL* __restrict__ wc = a.wc;
+
+    bool xact, yact, zact;
+    if (MODE == BMODE_MGPU) {
+        xact = (j >= 3 && j <= a.ny - 4) && (i >= 2 && i <= a.nx - 4);
+        yact = (i >= 3 && i <= a.nx - 4) && (j >= 2 && j <= a.ny - 4);
+        zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
+    } else {
+        xact = yact = zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
+    }
+    const bool x_seed0 = (MODE == BMODE_MGPU) && i == 2;     // f_old = 0 at the first marched cell
+    const bool y_seed0 = (MODE == BMODE_MGPU) && j == 2;
+    const bool rowacc_cell = (MODE == BMODE_MGPU) && j == 2 && yact && in_dom;
+
+    long long pre_off[NPRE];
+    bool pre_ok[NPRE];
+#pragma unroll
+    for (int n = 0; n < NPRE; n++) {
+        const int idx = tid + n * NT;
+        const int r = idx / RP, c = idx - r * RP;
+        const int gi = i0 - H + c, gj = j0 - H + r;
+        pre_ok[n] = idx < NPTS && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
+        pre_off[n] = (long long)gi + P * gj;
+    }
+    REAL pre[NPRE];
+    auto fetch = [&](int p) {
+        const bool pl = (p >= 0 && p < a.nzs);
+#pragma unroll
+        for (int n = 0; n < NPRE; n++) pre[n] = (pl && pre_ok[n]) ? u[pre_off[n] + Z * p] : REAL(0);
+    };
+    auto park = [&](int sidx) {
+#pragma unroll
+        for (int n = 0; n < NPRE; n++) {
+            const int idx = tid + n * NT;
+            if (idx < NPTS) {
+                const REAL v = pre[n], sq = v * v;
+                V2 r;
+                r.x = (v >= 0 ? wc[14] : -wc[15]) * sq;
+                r.y = (v >= 0 ? -wc[15] : wc[14]) * sq;
+                sm.slot[sidx][idx] = r;
+            }
+        }
+    };
+    const int own = (ty + H) * RP + tx + H;       // this thread's cell inside a slot (compute warps)
+
+    // ---- prologue: planes kb-3..kb+2 -> slots 0..5, lower z face of plane kb
+    for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
+    __syncthreads();
+    REAL Fz_prev = REAL(0);
+    if (!edge_warp) {
+        const V2 v0 = sm.slot[0][own], v1 = sm.slot[1][own], v2 = sm.slot[2][own], v3 = sm.slot[3][own],
+                 v4 = sm.slot[4][own], v5 = sm.slot[5][own];
+        Fz_prev = weno_side_c<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_c<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
+    }
+
+    REAL X1 = REAL(0), X2 = REAL(0);              // x face sums of the plane produced last iteration
+    REAL u_nxt = REAL(0), uo_nxt = REAL(0);       // own-cell u / uo of plane m+1, fetched a plane ahead
+    if (in_dom) { u_nxt = u[col + Z * kb]; uo_nxt = (a.stage == 1) ? u_nxt : uo[col + Z * kb]; }
+    int s0 = 0;                                   // slot of plane m-2
+
+    for (int m = kb - 1; m < ke; m++) {
+        auto sl = [&](int d) -> const V2* { int t = s0 + d; t = t >= NSLOT ? t - NSLOT : t; return sm.slot[t]; };
+        const bool do_final = (m >= kb);
+        const bool own_m = (m >= a.own_lo && m < a.own_hi);
+        const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
+        const bool do_fetch = (m + 4 <= ke + 2);
+        const int eb = m & 1, nb = eb ^ 1;
+        if (do_fetch) fetch(m + 4);
+        const REAL u_m = u_nxt, uo_m = uo_nxt;
+        if (in_dom && m + 1 < ke) {
+            u_nxt = u[col + Z * (m + 1)];
+            uo_nxt = (a.stage == 1) ? u_nxt : uo[col + Z * (m + 1)];
+        }
+
+        if (!edge_warp) {
+            if (do_final) {
+                // (1) x/y divergence of plane m from the halves produced in the previous iteration
+                REAL Lu = REAL(0);
+                if (own_m) {
+                    const REAL fu = (tx == 31) ? X1 + sm.edge_hp_x[eb][ty] : X1;
+                    REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][ty] + X2 : X2;
+                    fu_old = x_seed0 ? REAL(0) : fu_old;
+                    const REAL Lx = -(fu - fu_old) * a.rdx;
+                    const REAL gu = sm.hn_y[eb][ty + 1][tx] + sm.hp_y[eb][ty + 2][tx];
+                    REAL gu_old = sm.hn_y[eb][ty][tx] + sm.hp_y[eb][ty + 1][tx];
+                    gu_old = y_seed0 ? REAL(0) : gu_old;
+                    const REAL Ly = (gu - gu_old) * a.rdy;
+                    Lu = xact ? Lx : REAL(0);
+                    Lu = yact ? Lu - Ly : Lu;
+                }
+                // (2) upper z face of plane m: hn(m) from planes m-2..m+2, hp(m+1) from m-1..m+3
+                REAL Fz = REAL(0);
+                if (m >= a.own_lo - 1 && m < a.own_hi) {
+                    const V2 v0 = sl(0)[own], v1 = sl(1)[own], v2 = sl(2)[own], v3 = sl(3)[own], v4 = sl(4)[own], v5 = sl(5)[own];
+                    Fz = weno_side_c<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_c<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
+                }
+                // (3) finish cell (i,j,m)
+                if (in_dom) {
+                    const long long o = col + Z * m;
+                    const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && zact);
+                    if (own_m) {
+                        if (rowacc_cell) {
+                            const long long ra = (long long)i + P * m;
+                            if (a.stage > 1) Lu += rowacc[ra];
+                            rowacc[ra] = Lu;
+                        }
+                        Lu = zact ? Lu - (Fz - Fz_prev) * a.rdz : Lu;
+                    }
+                    const REAL t = u_m + a.dt * Lu;
+                    const REAL r1 = uo_m + a.dt * Lu;
+                    const REAL r2 = wc[14] * uo_m + wc[15] * t;
+                    const REAL r3 = (uo_m + REAL(2) * t) * wc[19];
+                    const REAL res = (a.stage == 1) ? r1 : (a.stage == 2) ? r2 : r3;
+                    out[o] = rk ? res : u_m;
+                }
+                Fz_prev = Fz;
+            }
+            // (4) halves of plane m+1 for the next iteration
+            if (do_pairs) {
+                const V2* __restrict__ s3 = sl(3);
+                const V2 c = s3[own];
+                const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
+                const REAL hn_x = weno_side_c<REAL, W>(xm2.x, xm1.x, c.x, xp1.x, xp2.x, wc);
+                const REAL hp_x = weno_side_c<REAL, W>(xp2.y, xp1.y, c.y, xm1.y, xm2.y, wc);
+                const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
+                sm.hn_y[nb][ty + 1][tx] = weno_side_c<REAL, W>(ym2.x, ym1.x, c.x, yp1.x, yp2.x, wc);
+                sm.hp_y[nb][ty + 1][tx] = weno_side_c<REAL, W>(yp2.y, yp1.y, c.y, ym1.y, ym2.y, wc);
+                const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
+                const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
+                X1 = (tx == 31) ? hn_x : hn_x + hpR;       // f_{i+1/2} = hn(i) + hp(i+1)
+                X2 = (tx == 0) ? hp_x : hnL + hp_x;        // f_{i-1/2} = hn(i-1) + hp(i)
+            }
+        } else if (do_pairs) {
+            const V2* __restrict__ s3 = sl(3);
+#pragma unroll 1
+            for (int it = tx; it < 2 * (TX + TY); it += 32) {
+                int oc, st;
+                bool minus;
+                if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
+                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
+                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
+                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
+                const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
+                const REAL v = weno_side_c<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
+                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
+                if (it < TY) sm.edge_hn_x[nb][it] = v;
+                else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
+                else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
+                else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
+            }
+        }
+        // (5) stage plane m+4 into the slot plane m-3 used to occupy
+        if (do_fetch) { int t = s0 + 6; t = t >= NSLOT ? t - NSLOT : t; park(t); }
+        __syncthreads();
+        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
+    }
+}
+
 }  // namespace adv

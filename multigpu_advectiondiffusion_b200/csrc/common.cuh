@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <math.h>
 
 namespace adv {
 
@@ -51,6 +52,26 @@ struct BurgersArgs {
     REAL dt, rdx, rdy, rdz;   // spacings passed as given (division kept as in the reference)
     REAL dx, dy, dz;
     REAL kx, ky, kz;
+    // WENO constants read straight from the kernel-parameter constant bank (no immediate moves):
+    // [0..2] r_k*13/12, [3..5] r_k/4, [6..8] r_k*eps with r_k = 1/sqrt(d_k) (JS) or 1 (Z);
+    // [9] 2/6 [10] 7/6 [11] 11/6 [12] 1/6 [13] 5/6 [14] 0.75 [15] 0.25 [16..18] d_k = .1 .6 .3 [19] 1/3
+    REAL wc[20];
 };
+
+template <typename REAL>
+inline void fill_weno_consts(BurgersArgs<REAL>& b, int weno)
+{
+    const double d[3] = {0.1, 0.6, 0.3};
+    for (int k = 0; k < 3; k++) {
+        const double r = weno == WENO_JS ? 1.0 / sqrt(d[k]) : 1.0;
+        b.wc[k] = (REAL)(r * 13.0 / 12.0);
+        b.wc[3 + k] = (REAL)(r * 0.25);
+        b.wc[6 + k] = (REAL)(r * 1e-6);
+        b.wc[16 + k] = (REAL)d[k];
+    }
+    b.wc[9] = (REAL)(2.0 / 6); b.wc[10] = (REAL)(7.0 / 6); b.wc[11] = (REAL)(11.0 / 6);
+    b.wc[12] = (REAL)(1.0 / 6); b.wc[13] = (REAL)(5.0 / 6); b.wc[14] = (REAL)0.75; b.wc[15] = (REAL)0.25;
+    b.wc[19] = (REAL)(1.0 / 3.0);
+}
 
 }  // namespace adv
