@@ -7,9 +7,9 @@ for v in ${VARIANTS:-ring1 ring2 tiled0}; do
   unset ADV_BURGERS_DIRECT ADV_BURGERS_VARIANT ADV_BURGERS_RING
   case $v in
     direct) export ADV_BURGERS_DIRECT=1;;
-    ring1) export ADV_BURGERS_RING=1;;
-    ring2) export ADV_BURGERS_RING=2;;
+    ring*) export ADV_BURGERS_RING=${v#ring};;
     tiled*) export ADV_BURGERS_RING=0 ADV_BURGERS_VARIANT=${v#tiled};;
   esac
+  python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
   run "variant=$v"
 done
