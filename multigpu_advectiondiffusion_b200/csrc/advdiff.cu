@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <new>
+#include <stdint.h>
 #include <vector>
 
 #include "burgers_kernels.cuh"
@@ -113,6 +114,57 @@ static int heat_args_from(const adv_stage_args* a, HeatArgs<REAL>& h)
     return ADV_OK;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver-entry-point lookup (no libcuda link dependency)
+typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn get_tmap_encode()
+{
+    static tmap_encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (tmap_encode_fn)p;
+    }
+    return fn;
+}
+
+template <typename REAL, int TY, int NST>
+static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+{
+    typedef HeatTmaSmem<REAL, TY, NST> S;
+    tmap_encode_fn enc = get_tmap_encode();
+    if (!enc) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    CUtensorMap tm;
+    const cuuint64_t gdim[3] = {(cuuint64_t)a->nx, (cuuint64_t)a->ny, (cuuint64_t)a->nzs};
+    const cuuint64_t gstr[2] = {(cuuint64_t)a->pitch * sizeof(REAL), (cuuint64_t)a->pitch * a->ny * sizeof(REAL)};
+    const cuuint32_t box[3] = {(cuuint32_t)S::BX, (cuuint32_t)S::BY, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&tm, sizeof(REAL) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)u_in,
+                     gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    const int planes = a->k_end - a->k_begin;
+    const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + TY - 1) / TY;
+    int nch = (2368 + gx * gy - 1) / (gx * gy);             // ~4 waves of 4 CTAs/SM on 148 SMs
+    if (nch > planes / 16) nch = planes / 16;               // 4 planes of z run-in per chunk
+    if (nch < 1) nch = 1;
+    const int chunk = (planes + nch - 1) / nch;
+    dim3 grid(gx, gy, (planes + chunk - 1) / chunk), block(32, TY, 1);
+    const size_t shm = sizeof(S);
+#define HEAT_TMA_LAUNCH(STAGE_) do { \
+        auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_>; \
+        if (shm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
+        kfn<<<grid, block, shm, st>>>(tm, h, chunk, uo, u_out); } while (0)
+    if (a->stage == 1) HEAT_TMA_LAUNCH(1); else if (a->stage == 2) HEAT_TMA_LAUNCH(2); else HEAT_TMA_LAUNCH(3);
+#undef HEAT_TMA_LAUNCH
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
 template <typename REAL>
 static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
 {
@@ -123,6 +175,18 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     HeatArgs<REAL> h;
     rc = heat_args_from<REAL>(a, h);
     if (rc) return rc;
+    // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
+    static const int heat_variant = getenv("ADV_HEAT_VARIANT") ? atoi(getenv("ADV_HEAT_VARIANT")) : 1;
+    const size_t vec = 16 / sizeof(REAL);
+    const bool tma_ok = heat_variant > 0 && (a->nx % 2 == 0) && (a->pitch % vec == 0) && a->nx >= 8 &&
+                        ((uintptr_t)u_in % 16 == 0) && ((uintptr_t)u_out % 16 == 0) && (a->stage == 1 || (uintptr_t)uo % 16 == 0) &&
+                        get_tmap_encode() != nullptr;
+    if (tma_ok) {
+        if (heat_variant == 2) return heat3d_launch_tma<REAL, 16, 4>(a, h, u_in, uo, u_out, st);
+        if (heat_variant == 3) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
+        if (heat_variant == 4) return heat3d_launch_tma<REAL, 4, 6>(a, h, u_in, uo, u_out, st);
+        return heat3d_launch_tma<REAL, 8, 4>(a, h, u_in, uo, u_out, st);
+    }
     constexpr int CHUNK = 32;
     dim3 block(32, 8, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
