@@ -165,6 +165,49 @@ static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, c
     return ADV_OK;
 }
 
+static int encode_tmap3(CUtensorMap* tm, int esz, const void* base, int nx, int ny, int nz, size_t pitch, int bx, int by)
+{
+    tmap_encode_fn enc = get_tmap_encode();
+    if (!enc) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t gdim[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz};
+    const cuuint64_t gstr[2] = {(cuuint64_t)pitch * esz, (cuuint64_t)pitch * ny * esz};
+    const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, esz == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base,
+                     gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return ADV_OK;
+}
+
+template <typename REAL, int TY, int NST>
+static int heat3d_launch_tma2(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+{
+    typedef HeatTma2Smem<REAL, TY, NST> S;
+    CUtensorMap tm, tmo;
+    int rc = encode_tmap3(&tm, sizeof(REAL), u_in, a->nx, a->ny, a->nzs, a->pitch, S::BX, S::BY);
+    if (rc) return rc;
+    rc = encode_tmap3(&tmo, sizeof(REAL), a->stage == 1 ? u_in : uo, a->nx, a->ny, a->nzs, a->pitch, S::TX, TY);
+    if (rc) return rc;
+    const int planes = a->k_end - a->k_begin;
+    const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + TY - 1) / TY;
+    static const int nch_env = getenv("ADV_HEAT_NCH") ? atoi(getenv("ADV_HEAT_NCH")) : 0;
+    int nch = nch_env > 0 ? nch_env : (2368 + gx * gy - 1) / (gx * gy);
+    if (nch > planes / 16) nch = planes / 16;
+    if (nch < 1) nch = 1;
+    const int chunk = (planes + nch - 1) / nch;
+    dim3 grid(gx, gy, (planes + chunk - 1) / chunk), block(32, TY + 1, 1);
+    const size_t shm = sizeof(S);
+#define HEAT_TMA2_LAUNCH(STAGE_) do { \
+        auto kfn = heat3d_stage_tma2<REAL, TY, NST, STAGE_>; \
+        if (shm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
+        kfn<<<grid, block, shm, st>>>(tm, tmo, h, chunk, u_out); } while (0)
+    if (a->stage == 1) HEAT_TMA2_LAUNCH(1); else if (a->stage == 2) HEAT_TMA2_LAUNCH(2); else HEAT_TMA2_LAUNCH(3);
+#undef HEAT_TMA2_LAUNCH
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
 template <typename REAL>
 static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
 {
@@ -176,12 +219,16 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     rc = heat_args_from<REAL>(a, h);
     if (rc) return rc;
     // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
-    static const int heat_variant = getenv("ADV_HEAT_VARIANT") ? atoi(getenv("ADV_HEAT_VARIANT")) : 1;
+    static const int heat_variant = getenv("ADV_HEAT_VARIANT") ? atoi(getenv("ADV_HEAT_VARIANT")) : 10;
     const size_t vec = 16 / sizeof(REAL);
     const bool tma_ok = heat_variant > 0 && (a->nx % 2 == 0) && (a->pitch % vec == 0) && a->nx >= 8 &&
                         ((uintptr_t)u_in % 16 == 0) && ((uintptr_t)u_out % 16 == 0) && (a->stage == 1 || (uintptr_t)uo % 16 == 0) &&
                         get_tmap_encode() != nullptr;
     if (tma_ok) {
+        if (heat_variant == 10) return heat3d_launch_tma2<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
+        if (heat_variant == 11) return heat3d_launch_tma2<REAL, 8, 8>(a, h, u_in, uo, u_out, st);
+        if (heat_variant == 12) return heat3d_launch_tma2<REAL, 4, 8>(a, h, u_in, uo, u_out, st);
+        if (heat_variant == 13) return heat3d_launch_tma2<REAL, 16, 6>(a, h, u_in, uo, u_out, st);
         if (heat_variant == 2) return heat3d_launch_tma<REAL, 16, 4>(a, h, u_in, uo, u_out, st);
         if (heat_variant == 3) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
         if (heat_variant == 4) return heat3d_launch_tma<REAL, 4, 6>(a, h, u_in, uo, u_out, st);

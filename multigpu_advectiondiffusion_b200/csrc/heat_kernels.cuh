@@ -249,4 +249,175 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, HeatArgs<REAL> a, int
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// v3 ("tma, warp-specialised"): the TMA kernel as a producer/consumer pipeline.
+//   - one producer warp (a single elected lane) keeps NST planes in flight: per plane ONE 3-D TMA box
+//     of u (tile + halo 2) and, for stages 2 and 3, one box of uo (tile only), both completing on the
+//     stage's `full` mbarrier; it refills a slot as soon as the consumers' `empty` mbarrier fires;
+//   - TY consumer warps never meet at a CTA barrier: wait(full) -> stencil -> arrive(empty);
+//   - the 5-plane z queue rotates by register renaming (loop unrolled 5x), no moves;
+//   - tiles inside the update region run without per-cell masks.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_arrive_(unsigned bar)
+{
+    asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(bar) : "memory");
+}
+
+template <typename REAL, int TY, int NST>
+struct HeatTma2Smem {
+    static constexpr int TX = 64, H = 2;
+    static constexpr int HX = (sizeof(REAL) == 8) ? 2 : 4;
+    static constexpr int BX = TX + 2 * HX, BY = TY + 2 * H;
+    struct alignas(128) Plane { REAL v[BY][BX]; };
+    struct alignas(128) Tile { REAL v[TY][TX]; };
+    Plane stage[NST];
+    Tile old[NST];
+    unsigned long long full[NST], empty[NST];
+};
+
+template <typename REAL, int TY, int NST, int STAGE>
+__global__ void __launch_bounds__(32 * (TY + 1))
+heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_uo,
+                  HeatArgs<REAL> a, int chunk, REAL* __restrict__ out)
+{
+    typedef typename Vec2T<REAL>::type V2;
+    typedef HeatTma2Smem<REAL, TY, NST> S;
+    constexpr int TX = S::TX, H = S::H, HX = S::HX, BX = S::BX, BY = S::BY;
+    constexpr unsigned kBytesU = BX * BY * sizeof(REAL), kBytesO = TX * TY * sizeof(REAL);
+    extern __shared__ __align__(128) unsigned char heat2_smem_raw[];
+    S& sm = *reinterpret_cast<S*>(heat2_smem_raw);
+
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+    const int kb = a.kb + blockIdx.z * chunk;
+    const int ke = min(kb + chunk, a.ke);
+    if (kb >= ke) return;
+    const int p_first = kb - 2;
+    const int N = (ke + 1) - p_first + 1;                   // planes to stream: kb-2 .. ke+1
+
+    if (tx == 0 && ty == 0) {
+        for (int s = 0; s < NST; s++) {
+            mbar_init_((unsigned)__cvta_generic_to_shared(&sm.full[s]), 1);
+            mbar_init_((unsigned)__cvta_generic_to_shared(&sm.empty[s]), TY);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (ty == TY) {
+        // ---------------- producer warp ----------------
+        if (tx == 0) {
+            for (int n = 0; n < N; n++) {
+                const int s = n % NST;
+                if (n >= NST) mbar_wait_parity((unsigned)__cvta_generic_to_shared(&sm.empty[s]), ((n / NST) - 1) & 1);
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.full[s]);
+                const int p = p_first + n, k = p - 2;
+                const bool with_old = (STAGE > 1) && (k >= kb) && (k < ke);
+                mbar_expect_tx(bar, with_old ? kBytesU + kBytesO : kBytesU);
+                tma_load_3d((unsigned)__cvta_generic_to_shared(&sm.stage[s].v[0][0]), &tmap, i0 - HX, j0 - H, p, bar);
+                if (with_old) tma_load_3d((unsigned)__cvta_generic_to_shared(&sm.old[s].v[0][0]), &tmap_uo, i0, j0, k, bar);
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumer warps ----------------
+    const int i = i0 + 2 * tx, j = j0 + ty;
+    const bool in_dom = (i < a.nx) && (j < a.ny);
+    const long long col = (long long)i + a.pitch * j;
+    const bool interior = i0 >= a.lap.lo[0] && i0 + TX - 1 <= a.lap.hi[0] && j0 >= a.lap.lo[1] && j0 + TY - 1 <= a.lap.hi[1] &&
+                          i0 >= a.rk.lo[0] && i0 + TX - 1 <= a.rk.hi[0] && j0 >= a.rk.lo[1] && j0 + TY - 1 <= a.rk.hi[1];
+    const bool xl0 = i >= a.lap.lo[0] && i <= a.lap.hi[0], xl1 = i + 1 >= a.lap.lo[0] && i + 1 <= a.lap.hi[0];
+    const bool yl = j >= a.lap.lo[1] && j <= a.lap.hi[1];
+    const bool xr0 = i >= a.rk.lo[0] && i <= a.rk.hi[0], xr1 = i + 1 >= a.rk.lo[0] && i + 1 <= a.rk.hi[0];
+    const bool yr = j >= a.rk.lo[1] && j <= a.rk.hi[1];
+    const REAL ciso = a.kx / REAL(12);
+    REAL* po = out + col + a.plane * (kb - 1);              // bumped before each store: plane k
+
+    auto lap = [&](const V2& zm2, const V2& zm1, const V2& zc, const V2& zp1, const V2& zp2, const REAL* row, V2& Lu) {
+        const V2 xl = *reinterpret_cast<const V2*>(row - 2), xr = *reinterpret_cast<const V2*>(row + 2);
+        const V2 ym2 = *reinterpret_cast<const V2*>(row - 2 * BX), ym1 = *reinterpret_cast<const V2*>(row - BX);
+        const V2 yp1 = *reinterpret_cast<const V2*>(row + BX), yp2 = *reinterpret_cast<const V2*>(row + 2 * BX);
+        if (a.iso) {
+            Lu.x = ciso * (-xl.x + REAL(16) * xl.y + REAL(16) * zc.y - xr.x
+                           - ym2.x + REAL(16) * ym1.x - REAL(90) * zc.x + REAL(16) * yp1.x - yp2.x
+                           - zm2.x + REAL(16) * zm1.x + REAL(16) * zp1.x - zp2.x);
+            Lu.y = ciso * (-xl.y + REAL(16) * zc.x + REAL(16) * xr.x - xr.y
+                           - ym2.y + REAL(16) * ym1.y - REAL(90) * zc.y + REAL(16) * yp1.y - yp2.y
+                           - zm2.y + REAL(16) * zm1.y + REAL(16) * zp1.y - zp2.y);
+        } else {
+            Lu.x = a.kx * (-xl.x + REAL(16) * xl.y - REAL(30) * zc.x + REAL(16) * zc.y - xr.x) +
+                   a.ky * (-ym2.x + REAL(16) * ym1.x - REAL(30) * zc.x + REAL(16) * yp1.x - yp2.x) +
+                   a.kz * (-zm2.x + REAL(16) * zm1.x - REAL(30) * zc.x + REAL(16) * zp1.x - zp2.x);
+            Lu.y = a.kx * (-xl.y + REAL(16) * zc.x - REAL(30) * zc.y + REAL(16) * xr.x - xr.y) +
+                   a.ky * (-ym2.y + REAL(16) * ym1.y - REAL(30) * zc.y + REAL(16) * yp1.y - yp2.y) +
+                   a.kz * (-zm2.y + REAL(16) * zm1.y - REAL(30) * zc.y + REAL(16) * zp1.y - zp2.y);
+        }
+    };
+
+    int n = 0;
+    // one plane: `nw` receives plane p (it held the dead plane p-5); stencil planes are zm2..zp1, nw
+    auto step = [&](V2& nw, const V2& zm2, const V2& zm1, const V2& zc, const V2& zp1) -> bool {
+        if (n >= N) return false;
+        const int s = n % NST;
+        mbar_wait_parity((unsigned)__cvta_generic_to_shared(&sm.full[s]), (n / NST) & 1);
+        nw = *reinterpret_cast<const V2*>(&sm.stage[s].v[ty + H][2 * tx + HX]);
+        const int k = p_first + n - 2;
+        if (k >= kb) {
+            const int sk = (n - 2) % NST;
+            po += a.plane;
+            const bool zl = k >= a.lap.lo[2] && k <= a.lap.hi[2];
+            const bool zr = k >= a.rk.lo[2] && k <= a.rk.hi[2];
+            V2 qo = zc;
+            if (STAGE > 1) qo = *reinterpret_cast<const V2*>(&sm.old[s].v[ty][2 * tx]);
+            V2 res = zc;
+            const REAL* row = &sm.stage[sk].v[ty + H][2 * tx + HX];
+            if (interior) {
+                if (zr) {
+                    V2 Lu;
+                    Lu.x = Lu.y = REAL(0);
+                    if (zl) lap(zm2, zm1, zc, zp1, nw, row, Lu);
+                    res.x = rk_combine<REAL>(STAGE, zc.x, qo.x, Lu.x, a.dt);
+                    res.y = rk_combine<REAL>(STAGE, zc.y, qo.y, Lu.y, a.dt);
+                }
+                *reinterpret_cast<V2*>(po) = res;
+            } else {
+                if (yr && zr) {
+                    V2 Lu;
+                    Lu.x = Lu.y = REAL(0);
+                    if (yl && zl) {
+                        lap(zm2, zm1, zc, zp1, nw, row, Lu);
+                        Lu.x = xl0 ? Lu.x : REAL(0);
+                        Lu.y = xl1 ? Lu.y : REAL(0);
+                    }
+                    const REAL r0 = rk_combine<REAL>(STAGE, zc.x, qo.x, Lu.x, a.dt);
+                    const REAL r1 = rk_combine<REAL>(STAGE, zc.y, qo.y, Lu.y, a.dt);
+                    res.x = xr0 ? r0 : zc.x;
+                    res.y = xr1 ? r1 : zc.y;
+                }
+                if (in_dom) *reinterpret_cast<V2*>(po) = res;
+            }
+        }
+        if (n >= 2) {
+            // the plane staged two iterations ago has served as centre plane (or never will: the two
+            // run-in planes below the chunk): its slot goes back to the producer
+            __syncwarp();
+            if (tx == 0) mbar_arrive_((unsigned)__cvta_generic_to_shared(&sm.empty[(n - 2) % NST]));
+        }
+        n++;
+        return true;
+    };
+
+    V2 q0, q1, q2, q3, q4;
+    q0.x = q0.y = q1.x = q1.y = q2.x = q2.y = q3.x = q3.y = q4.x = q4.y = REAL(0);
+    for (;;) {
+        if (!step(q0, q1, q2, q3, q4)) break;
+        if (!step(q1, q2, q3, q4, q0)) break;
+        if (!step(q2, q3, q4, q0, q1)) break;
+        if (!step(q3, q4, q0, q1, q2)) break;
+        if (!step(q4, q0, q1, q2, q3)) break;
+    }
+}
+
 }  // namespace adv

@@ -1,0 +1,145 @@
+"""Worker for the multi-rank tests (one process per rank).
+
+mode `cpu`  (gloo, no GPU): emulates the z-slab time stepping on the CPU with the oracle's RHS and
+            exchanges the stage OUTPUT u planes (what libadvdiff ships) instead of the reference's Lu
+            planes; rank 0 checks the merged result bit-for-bit against the oracle's whole-domain run.
+mode `gpu`  (nccl): every rank drives its GPU through the C ABI (adv_create with nranks/rank/comm_id),
+            rank 0 merges the slabs and checks them bit-for-bit against a 1-rank GPU run and to 1e-12
+            against the oracle.
+Prints `MP_OK ...` on success.
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import oracle as orc  # noqa: E402
+
+
+def slab_bounds(nz, P, r):
+    nzl = nz // P
+    return r * nzl, r * nzl + nzl + 6          # global planes [g0, g1) stored by rank r (Tools.c:181-200)
+
+
+def exchange_cpu(u, rank, P):
+    """send planes [3,6) left and [nzs-6,nzs-3) right; receive into [nzs-3,nzs) and [0,3)."""
+    reqs = []
+    nzs = u.shape[0]
+    if rank < P - 1:
+        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(u[nzs - 6:nzs - 3])), rank + 1, tag=1))
+    if rank > 0:
+        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(u[3:6])), rank - 1, tag=5))
+    if rank < P - 1:
+        buf = torch.empty(u[nzs - 3:].shape, dtype=torch.float64)
+        dist.recv(buf, rank + 1, tag=5)
+        u[nzs - 3:] = buf.numpy()
+    if rank > 0:
+        buf = torch.empty(u[:3].shape, dtype=torch.float64)
+        dist.recv(buf, rank - 1, tag=1)
+        u[:3] = buf.numpy()
+    for q in reqs:
+        q.wait()
+
+
+def run_cpu(rank, P, nx, ny, nz, nsteps):
+    L = orc.lib()
+    L.orc_burgers3d_mgpu_rhs_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double]
+    L.orc_burgers3d_mgpu_rhs_f64.restype = None
+    g = orc.ic_burgers3d_mgpu(nx, ny, nz)
+    dx, dy, dz = 2.0 / (nx - 1), 2.0 / (ny - 1), 2.0 / (nz - 1)
+    dt = 0.3 * dx
+    g0, g1 = slab_bounds(nz, P, rank)
+    u = g[g0:g1].copy()
+    nzs = u.shape[0]
+    for _ in range(nsteps):
+        uo = u.copy()
+        Lu = np.zeros_like(u)
+        for stage in (1, 2, 3):
+            L.orc_burgers3d_mgpu_rhs_f64(u.ctypes.data, Lu.ctypes.data, nx, ny, nzs, dx, dy, dz)
+            if stage == 1:
+                new = uo + dt * Lu
+            elif stage == 2:
+                new = 0.75 * uo + 0.25 * (u + dt * Lu)
+            else:
+                new = (uo + 2 * (u + dt * Lu)) / 3
+            # ghost planes that a neighbour owns are not ours to advance: they arrive by exchange
+            lo = 0 if rank == 0 else 3
+            hi = nzs if rank == P - 1 else nzs - 3
+            u[lo:hi] = new[lo:hi]
+            exchange_cpu(u, rank, P)
+    parts = [None] * P if rank == 0 else None
+    dist.gather_object(u, parts, dst=0)
+    if rank == 0:
+        merged = g.copy()
+        nzl = nz // P
+        for r in range(P):
+            merged[r * nzl + 3: r * nzl + 3 + nzl] = parts[r][3:3 + nzl]
+        want, _ = orc.burgers3d_mgpu(g, 1e9, max_steps=nsteps)
+        assert np.array_equal(merged, want), float(np.abs(merged - want).max())
+        print("MP_OK cpu P=%d bit-exact vs oracle" % P)
+
+
+def run_gpu(rank, P, target, nx, ny, nz, nsteps):
+    import multigpu_advectiondiffusion_b200 as adv
+    torch.cuda.set_device(rank)
+    idb = [None]
+    if rank == 0:
+        buf = (C.c_ubyte * 128)()
+        adv._lib.check(adv.lib().adv_comm_unique_id(C.byref(buf)))
+        idb = [bytes(buf)]
+    dist.broadcast_object_list(idb, 0)
+    coef = 0.3 if "burgers" in target else 1.0
+    g = orc.ic_burgers3d_mgpu(nx, ny, nz) if "burgers" in target else orc.ic_heat3d_mgpu(nx, ny, nz)
+    g0, g1 = slab_bounds(nz, P, rank)
+    with adv.Solver(target, nx, ny, nz, coef=coef, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
+        # the library's own IC slicing must equal Init_subdomain of the reference IC
+        s.init_reference_ic()
+        assert np.array_equal(s.download(), g[g0:g1]), "rank %d: IC slab differs" % rank
+        s.step(nsteps)
+        s.sync()
+        u = s.download()
+    parts = [None] * P if rank == 0 else None
+    dist.gather_object(u, parts, dst=0)
+    if rank == 0:
+        merged = g.copy()
+        nzl = nz // P
+        for r in range(P):
+            merged[r * nzl + 3: r * nzl + 3 + nzl] = parts[r][3:3 + nzl]
+        with adv.Solver(target, nx, ny, nz, coef=coef, device=0) as s1:
+            s1.upload(g)
+            s1.step(nsteps)
+            one = s1.download()
+        one[:3], one[-3:] = g[:3], g[-3:]
+        assert np.array_equal(merged, one), "P=%d differs from P=1 on the GPU: %g" % (P, float(np.abs(merged - one).max()))
+        if "burgers" in target:
+            want, _ = orc.burgers3d_mgpu(g, 1e9, max_steps=nsteps)
+        else:
+            want, _ = orc.heat3d(g, nsteps, "mgpu", L=2.0, W=2.0, H=2.0)
+        err = orc.rel_err(merged, want)
+        assert err <= 1e-12, err
+        print("MP_OK gpu %s P=%d bit-exact vs P=1, rel err vs oracle %.2e" % (target, P, err))
+
+
+def main():
+    mode = sys.argv[1]
+    rank, P = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dist.init_process_group("gloo" if mode == "cpu" else "nccl",
+                            **({} if mode == "cpu" else {"device_id": torch.device("cuda", rank)}))
+    try:
+        if mode == "cpu":
+            run_cpu(rank, P, 20, 22, 24, 2)
+        else:
+            for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5)):
+                run_gpu(rank, P, target, *shape, steps)
+    finally:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
