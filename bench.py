@@ -52,52 +52,65 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(workload):
-    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+def ncu_profile(workload):
+    """Per-launch numbers of the dominant kernel from the committed ncu --set full capture
+    (profiles/traffic.json, written by the summary step in profiles/README.md)."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(workload)
+            d = json.load(open(p))
+            return d.get(workload), d.get("fp64_peak")
         except Exception:
-            return None
-    return None
+            pass
+    return None, None
 
 
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md)."""
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons every 50 ms while the timed region runs (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        super().__init__(daemon=True)
         self.index = index
-        self.rows = []
-        self.stop_flag = threading.Event()
+        self.proc = None
 
-    def run(self):
-        while not self.stop_flag.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            self.stop_flag.wait(0.2)
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            time.sleep(0.15)            # let the first sample land before the timed region starts
+        except Exception:
+            self.proc = None
 
     def summary(self):
-        self.stop_flag.set()
-        self.join(timeout=6)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        rows = []
+        if self.proc is not None:
+            time.sleep(0.06)
+            self.proc.terminate()
+            try:
+                out, _ = self.proc.communicate(timeout=5)
+            except Exception:
+                self.proc.kill()
+                out = ""
+            rows = [[x.strip() for x in ln.split(",")] for ln in out.splitlines() if ln.strip()]
+
+        def num(x):
+            try:
+                return float(x)
+            except ValueError:
+                return None
+        sm = [num(r[0]) for r in rows if num(r[0]) is not None]
+        mx = [num(r[1]) for r in rows if len(r) > 1 and num(r[1]) is not None]
+        pw = [num(r[2]) for r in rows if len(r) > 2 and num(r[2]) is not None]
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in rows:
             for n, v in zip(names, r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.rows)}
+                "power_w_max": max(pw) if pw else None, "reasons": sorted(reasons), "samples": len(rows)}
 
 
 def cpu_sample(w, precision_bytes, target_seconds=12.0):
@@ -255,11 +268,22 @@ def main():
     per_launch_bytes = BYTES_PER_CELL_STEP[esz] / 3.0 * cells_local
     launch_s = ms * 1e-3 / (3 * args.steps)
     achieved = per_launch_bytes / launch_s / 1e9
+    prof, fp64_peak = ncu_profile(args.workload)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                "traffic": prof["dram_bytes_per_launch_mean"] if prof else None, "peak_source": peak_src,
                 "kernel": "burgers3d_stage" if "burgers" in w["target"] else "heat3d_stage",
                 "algorithmic_bytes_per_launch": per_launch_bytes,
                 "note": "FP64 WENO5 is bound by the FP64 pipe, not HBM (SURVEY F11); see DESIGN.md" if "burgers" in w["target"] and esz == 8 else ""}
+
+    # FP64 WENO5 is bound by the FP64 pipe: FP64 thread-instructions per launch (ncu capture of this workload)
+    # over the live launch time, against the measured DFMA peak (tools/fp64_peak.cu)
+    fp64 = None
+    if prof and fp64_peak and "burgers" in w["target"] and esz == 8:
+        inst = float(np.mean(prof["warp_inst_per_launch_stage123"])) * prof["fp64_share_of_inst_stage2"] * 32.0
+        fp64 = {"bound": "fp64-pipe", "achieved": inst / launch_s / 1e12, "peak": fp64_peak["fma_per_s"] / 1e12,
+                "unit": "T FP64 instr/s", "frac": inst / launch_s / fp64_peak["fma_per_s"],
+                "fp64_inst_per_cell_update": inst / cells_local,
+                "source": "ncu warp-instruction count x FP64 share (profiles/traffic.json) / live launch time; peak = measured DFMA rate"}
 
     # end to end through the solver API with host buffers: upload + S steps + download per e2e step
     e2e = None
@@ -297,7 +321,7 @@ def main():
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic", "config": config,
                 "hbm_gbs": achieved * (world if nranks > 1 or w["scaling"] == "replicas" else 1),
-                "roofline": roofline, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": roofline, "roofline_fp64": fp64, "cpu_baseline": cb, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks, "wall_s_timed_region": t_wall}
         print(json.dumps(line))
     if dist is not None:

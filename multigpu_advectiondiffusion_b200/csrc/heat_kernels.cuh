@@ -98,6 +98,16 @@ heat2d_stage_direct(HeatArgs<REAL> a, const REAL* __restrict__ u, const REAL* __
 
 namespace adv {
 
+// RK combine with the division by 3 of stage 3 written as a multiplication (an IEEE double division
+// costs ~25 FP64-pipe instructions per cell and made stage 3 compute-bound: 705 vs 505 us at 512^3)
+template <typename REAL, int STAGE>
+__device__ __forceinline__ REAL rk_combine_fast(REAL q, REAL qo, REAL Lq, REAL dt)
+{
+    if (STAGE == 1) return qo + dt * Lq;
+    if (STAGE == 2) return REAL(0.75) * qo + REAL(0.25) * (q + dt * Lq);
+    return (qo + REAL(2) * (q + dt * Lq)) * REAL(1.0 / 3.0);
+}
+
 template <typename REAL> struct Vec2T;
 template <> struct Vec2T<double> { typedef double2 type; };
 template <> struct Vec2T<float> { typedef float2 type; };
@@ -378,8 +388,8 @@ heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                     V2 Lu;
                     Lu.x = Lu.y = REAL(0);
                     if (zl) lap(zm2, zm1, zc, zp1, nw, row, Lu);
-                    res.x = rk_combine<REAL>(STAGE, zc.x, qo.x, Lu.x, a.dt);
-                    res.y = rk_combine<REAL>(STAGE, zc.y, qo.y, Lu.y, a.dt);
+                    res.x = rk_combine_fast<REAL, STAGE>(zc.x, qo.x, Lu.x, a.dt);
+                    res.y = rk_combine_fast<REAL, STAGE>(zc.y, qo.y, Lu.y, a.dt);
                 }
                 *reinterpret_cast<V2*>(po) = res;
             } else {
@@ -391,8 +401,8 @@ heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                         Lu.x = xl0 ? Lu.x : REAL(0);
                         Lu.y = xl1 ? Lu.y : REAL(0);
                     }
-                    const REAL r0 = rk_combine<REAL>(STAGE, zc.x, qo.x, Lu.x, a.dt);
-                    const REAL r1 = rk_combine<REAL>(STAGE, zc.y, qo.y, Lu.y, a.dt);
+                    const REAL r0 = rk_combine_fast<REAL, STAGE>(zc.x, qo.x, Lu.x, a.dt);
+                    const REAL r1 = rk_combine_fast<REAL, STAGE>(zc.y, qo.y, Lu.y, a.dt);
                     res.x = xr0 ? r0 : zc.x;
                     res.y = xr1 ? r1 : zc.y;
                 }
