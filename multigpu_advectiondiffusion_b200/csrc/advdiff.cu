@@ -289,9 +289,10 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
     static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 32;
-    if (mg && !force_direct && ring >= 30) {
-        // v6: specialised split-barrier ring kernel.  30: 32x8 CPT1 3 CTAs/SM; 32: 32x16 CPT2 2 CTAs/SM
-        const int TYv = (ring == 33) ? 14 : (ring == 34) ? 12 : (ring >= 32) ? 16 : 8;
+    if (!force_direct && ring >= 30) {
+        // v6: specialised split-barrier ring kernel.  30: 32x8 CPT1 3 CTAs/SM; 32 (default): 32x16 CPT2 2 CTAs/SM;
+        // 33: 32x14 CPT2 (256 threads, 128 registers)
+        const int TYv = !mg ? 16 : (ring == 33) ? 14 : (ring == 30) ? 8 : 16;
         const int planes = a->k_end - a->k_begin;
         const int gx = (a->nx + 31) / 32, gy = (a->ny + TYv - 1) / TYv;
         int nch = (1776 + gx * gy - 1) / (gx * gy);
@@ -300,19 +301,19 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         const int chunk = (planes + nch - 1) / nch;
         dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
-#define LAUNCH_RING4(TY_, CPT_, MINB_, STAGE_) do { \
-            auto kfn = burgers3d_stage_ring4<REAL, WENO_JS, BMODE_MGPU, TY_, CPT_, MINB_, STAGE_>; \
+#define LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, STAGE_) do { \
+            auto kfn = burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_>; \
             const size_t shm = sizeof(BurgersRing4Smem<REAL, TY_>); \
             CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
             kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
-#define LAUNCH_RING4_S(TY_, CPT_, MINB_) do { \
-            if (a->stage == 1) LAUNCH_RING4(TY_, CPT_, MINB_, 1); \
-            else if (a->stage == 2) LAUNCH_RING4(TY_, CPT_, MINB_, 2); \
-            else LAUNCH_RING4(TY_, CPT_, MINB_, 3); } while (0)
-        if (ring == 30) LAUNCH_RING4_S(8, 1, 3);
-        else if (ring == 33) LAUNCH_RING4_S(14, 2, 2);      // 7+1 warps = 256 threads: 128 registers at 2 CTAs/SM
-        else if (ring == 34) LAUNCH_RING4_S(12, 2, 3);      // 6+1 warps = 224 threads, 3 CTAs/SM
-        else LAUNCH_RING4_S(16, 2, 2);
+#define LAUNCH_RING4_S(W_, M_, TY_, CPT_, MINB_) do { \
+            if (a->stage == 1) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 1); \
+            else if (a->stage == 2) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 2); \
+            else LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 3); } while (0)
+        if (!mg) LAUNCH_RING4_S(WENO_Z, BMODE_SGPU, 16, 2, 2);
+        else if (ring == 30) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 8, 1, 3);
+        else if (ring == 33) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 14, 2, 2);
+        else LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 16, 2, 2);
 #undef LAUNCH_RING4_S
 #undef LAUNCH_RING4
     } else if (mg && !force_direct && ring >= 20) {

@@ -1312,6 +1312,13 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
         return weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
     };
 
+    // viscous 13-point term of the single-GPU target (Compute_Laplace_Async, SingleGPU/Burgers3d_WENO5/
+    // kernels.cu:471-473): needs u itself, which the ring does not hold -- read through L1/L2
+    auto visc13 = [&](const REAL* __restrict__ pc, REAL c0) -> REAL {
+        return a.kx * (-pc[-2] + 16 * pc[-1] - 30 * c0 + 16 * pc[1] - pc[2]) +
+               a.ky * (-pc[-2 * P] + 16 * pc[-P] - 30 * c0 + 16 * pc[P] - pc[2 * P]) +
+               a.kz * (-pc[-2 * Z] + 16 * pc[-Z] - 30 * c0 + 16 * pc[Z] - pc[2 * Z]);
+    };
     if (tid == 0) mbar_init(bar, NT);
     for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
     __syncthreads();
@@ -1376,6 +1383,11 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                             Lu = -(fu - fu_old) * a.rdx;
                             Lu -= (gu - gu_old) * a.rdy;
                             Lu -= (Fz[c] - Fz_prev[c]) * a.rdz;
+                            if (MODE == BMODE_SGPU && a.visc) {
+                                const REAL term = visc13(pu[c] - Z, u_m[c]);
+                                Lu += term;
+                                if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
+                            }
                         }
                         const bool rk = (MODE == BMODE_MGPU) ? true : own_m;
                         const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
@@ -1411,6 +1423,11 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                                     rowacc[ra] = Lu;
                                 }
                                 Lu = za ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz : Lu;
+                                if (MODE == BMODE_SGPU && a.visc && za) {
+                                    const REAL term = visc13(pu[c] - Z, u_m[c]);
+                                    Lu += term;
+                                    if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
+                                }
                             }
                             const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
                             *pout[c] = rk ? res : u_m[c];

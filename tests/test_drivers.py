@@ -1,0 +1,88 @@
+"""The plain-C drivers (drivers/*.c over include/advdiff.h): argv / usage behaviour on the CPU, and on
+the GPU the files and stdout a reference run would leave (result.bin / initial.bin: float32, headerless,
+x fastest, multi-GPU files padded to Nz+6 planes)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DRV = os.path.join(ROOT, "drivers")
+
+
+def _build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "multigpu_advectiondiffusion_b200")])
+    subprocess.check_call(["make", "-s", "-C", DRV])
+
+
+@pytest.mark.parametrize("exe,usage", [
+    ("burgers3d.run", "tEnd CFL L W H NX NY NZ block_x block_y block_z"),
+    ("diffusion3d.run", "diffCoef L W H NX NY NZ n_iter block_x block_y block_z"),
+    ("diffusion3d_blocking.run", "diffCoef L W H NX NY NZ n_iter"),
+    ("diffusion2d.run", "PO CFL L W NX NY n_iter block_x block_y"),
+    ("Burgers3d_mgpu.run", "tEnd CFL L W H Nx Ny NZ block_x block_y block_z"),
+    ("Diffusion3d_mgpu.run", "K L W H Nx Ny NZ max_iters block_x block_y block_z"),
+])
+def test_wrong_argc_prints_usage_and_exits_1(exe, usage):
+    """Reference behaviour: printf("Usage: ...") then exit(1) (e.g. MultiGPU/Burgers3d_Baseline/main.c:50-54)."""
+    _build()
+    r = subprocess.run([os.path.join(DRV, exe), "1", "2"], capture_output=True, text=True)
+    assert r.returncode == 1
+    assert r.stdout.startswith("Usage: ") and usage in r.stdout
+
+
+def test_drivers_fail_loudly_without_a_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    _build()
+    r = subprocess.run([os.path.join(DRV, "burgers3d.run")] + "0.1 0.3 2 2 2 32 32 32 8 8 8".split(), capture_output=True, text=True)
+    assert r.returncode != 0 and "adv_create" in r.stdout
+
+
+@pytest.mark.gpu
+def test_burgers3d_mgpu_driver_files(tmp_path):
+    _build()
+    nx, ny, nz = 40, 36, 48
+    args = ["0.05", "0.3", "2.0", "2.0", "2.0", str(nx), str(ny), str(nz), "8", "8", "8"]
+    r = subprocess.run([os.path.join(DRV, "Burgers3d_mgpu.run")] + args, capture_output=True, text=True, cwd=tmp_path, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "=======================Burgers-3D MPI-GPU-WENO5=====================" in r.stdout
+    assert "3D Grid Size                                 :  %d x %d x %d" % (nx, ny, nz + 6) in r.stdout
+    g = orc.ic_burgers3d_mgpu(nx, ny, nz)
+    want, info = orc.burgers3d_mgpu(g, 0.05)
+    assert "iterations: %g" % info["it"] in r.stdout
+    ini = np.fromfile(tmp_path / "initial.bin", dtype=np.float32)
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert ini.size == res.size == nx * ny * (nz + 6)
+    assert np.array_equal(ini, g.astype(np.float32).ravel())
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    # pad planes of result.bin hold the initial values
+    assert np.array_equal(res.reshape(nz + 6, ny, nx)[:3], g[:3].astype(np.float32))
+
+
+@pytest.mark.gpu
+def test_heat_and_sgpu_drivers(tmp_path):
+    _build()
+    r = subprocess.run([os.path.join(DRV, "diffusion3d.run")] + "1.0 10 10 10 40 36 32 5 32 4 4".split(),
+                       capture_output=True, text=True, cwd=tmp_path, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    want, _ = orc.heat3d(orc.ic_heat3d_sgpu(40, 36, 32), 5, "baseline")
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert res.size == 40 * 36 * 32 and np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    r = subprocess.run([os.path.join(DRV, "diffusion2d.run")] + "1.0 10 10 64 48 10 16 16".split(),
+                       capture_output=True, text=True, cwd=tmp_path, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    want, _ = orc.heat2d(orc.ic_heat2d_sgpu(64, 48), 10)
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert res.size == 64 * 48 and np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    env = dict(os.environ, ADV_WRITE="1")
+    r = subprocess.run([os.path.join(DRV, "burgers3d.run")] + "0.04 0.3 2 2 2 32 32 32 8 8 8".split(),
+                       capture_output=True, text=True, cwd=tmp_path, timeout=120, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    want, info = orc.burgers3d_sgpu(orc.ic_burgers3d_sgpu(32, 32, 32), 0.04)
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6 and "iterations: %g" % info["it"] in r.stdout
