@@ -9,8 +9,10 @@
 #include "common.h"
 
 #define RADIUS ADV_RADIUS
-typedef struct {
+typedef struct rank_ctx {
     adv_desc d;
+    adv_solver* solver;
+    struct rank_ctx* all;
     double tEnd;
     int iters;
     double* h_u;            /* global padded array (shared) */
@@ -28,6 +30,16 @@ static void* rank_main(void* p)
     c->rc = adv_create(&c->d, &s);
     if (c->rc) { printf("rank %d: %s\n", c->d.rank, adv_last_error()); exit(-1); }
     printf("Process %d -> GPU%d\n", c->d.rank, c->d.device);
+    /* all ranks live in this process: let the boundary kernels store into the neighbours' ghost planes
+     * directly (NVLink peer access); ADV_HALO=nccl keeps the ncclSend/ncclRecv path */
+    c->solver = s;
+    pthread_barrier_wait(c->bar);
+    if (c->d.nranks > 1 && !(getenv("ADV_HALO") && !strcmp(getenv("ADV_HALO"), "nccl"))) {
+        adv_solver* left = c->d.rank > 0 ? c->all[c->d.rank - 1].solver : NULL;
+        adv_solver* right = c->d.rank < c->d.nranks - 1 ? c->all[c->d.rank + 1].solver : NULL;
+        if (adv_peer_connect_local(s, left, right)) printf("rank %d: peer halo unavailable (%s), using NCCL\n", c->d.rank, adv_last_error());
+    }
+    pthread_barrier_wait(c->bar);
     const size_t n = adv_local_elems(s);
     double* h_s_u = (double*)malloc(sizeof(double) * n);
 
@@ -113,7 +125,7 @@ int main(int argc, char** argv)
         d->precision = ADV_F64; d->nx = Nx; d->ny = Ny; d->nz = Nz; d->lx = L; d->ly = W; d->lz = H;
         d->device = r; d->nranks = P; d->rank = r;
         memcpy(d->comm_id, id, 128);
-        ctx[r].h_u = h_u; ctx[r]._Nz = Nz / P; ctx[r].bar = &bar;
+        ctx[r].h_u = h_u; ctx[r]._Nz = Nz / P; ctx[r].bar = &bar; ctx[r].all = ctx;
     }
 #ifdef BURGERS
     printf("dx: %g, dy: %g, dz: %g, final time: %g\n\n", dx, dy, dz, a1);

@@ -139,6 +139,21 @@ long long adv_kernel_launches(const adv_solver* s);
 /* raw device pointer of the current solution buffer and its row pitch in elements */
 int  adv_device_field(adv_solver* s, void** dptr, size_t* pitch_elems);
 
+/* ---- fused halo exchange over NVLink peer memory (optional; default is NCCL send/recv) ------------ */
+/* replaces the reference's pack kernel + D2H + MPI_Isend/Irecv + H2D + unpack kernel per stage
+ * (MultiGPU/Burgers3d_Baseline/main.c:208-302, Kernels.cu:40-105): once connected, the boundary-slab stage
+ * kernels store their three planes straight into the neighbour GPU's ghost planes and a per-neighbour flag
+ * orders the stages; no communication kernel, no host involvement.  Results are bit-identical to the NCCL
+ * path.  Call on every rank, after adv_create and before stepping.
+ *   adv_peer_handle        64-byte CUDA IPC handle of this rank's device arena (ranks = processes)
+ *   adv_peer_connect       map the neighbours' arenas from their handles (NULL where there is no neighbour)
+ *   adv_peer_connect_local same for ranks that live in one process (plain-C multi-GPU drivers)
+ *   adv_halo_mode          0 single rank, 1 NCCL, 2 fused peer stores */
+int  adv_peer_handle(adv_solver* s, unsigned char handle[64]);
+int  adv_peer_connect(adv_solver* s, const unsigned char* left_handle, const unsigned char* right_handle);
+int  adv_peer_connect_local(adv_solver* s, adv_solver* left, adv_solver* right);
+int  adv_halo_mode(const adv_solver* s);
+
 /* One-call convenience used by the drivers: create + upload + run + download + destroy on host
  * buffers (whole padded domain, single rank).  Mirrors one run of a reference binary. */
 int  adv_solve_host(const adv_desc* desc, const void* host_in, void* host_out,

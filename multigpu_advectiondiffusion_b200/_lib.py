@@ -68,6 +68,10 @@ SIGNATURES = {
     "adv_last_elapsed_ms": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "adv_kernel_launches": (C.c_longlong, [_P]),
     "adv_device_field": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),
+    "adv_peer_handle": (C.c_int, [_P, C.POINTER(C.c_ubyte * 64)]),
+    "adv_peer_connect": (C.c_int, [_P, C.c_char_p, C.c_char_p]),
+    "adv_peer_connect_local": (C.c_int, [_P, _P, _P]),
+    "adv_halo_mode": (C.c_int, [_P]),
     "adv_solve_host": (C.c_int, [C.POINTER(Desc), _P, _P, C.c_double] + [C.POINTER(C.c_double)] * 3),
     "adv_heat3d_stage_f64": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
     "adv_heat3d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),

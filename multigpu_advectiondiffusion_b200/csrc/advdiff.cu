@@ -69,6 +69,10 @@ static bool is_heat(int t)
 }
 static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU; }
 
+// second destination of a stage launch (fused halo exchange); internal, not part of the public stage ABI
+struct PeerOut { void* out2; long long off2; };
+static const PeerOut kNoPeer = {nullptr, 0};
+
 static int check_stage_args(const adv_stage_args* a, const void* u_in, const void* uo, const void* u_out, int min_n)
 {
     if (!a || !u_in || !u_out) return fail(ADV_ERR_INVALID, "NULL argument");
@@ -83,6 +87,7 @@ static int check_stage_args(const adv_stage_args* a, const void* u_in, const voi
 template <typename REAL>
 static int heat_args_from(const adv_stage_args* a, HeatArgs<REAL>& h)
 {
+    h.out2 = nullptr; h.off2 = 0;
     h.nx = a->nx; h.ny = a->ny; h.nzs = a->nzs;
     h.pitch = (long long)a->pitch; h.plane = (long long)a->pitch * a->ny;
     h.kb = a->k_begin; h.ke = a->k_end;
@@ -209,7 +214,15 @@ static int heat3d_launch_tma2(const adv_stage_args* a, const HeatArgs<REAL>& h, 
 }
 
 template <typename REAL>
-static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+static bool heat3d_tma_ok(const adv_stage_args* a, const REAL* u_in, const REAL* uo, const REAL* u_out)
+{
+    const size_t vec = 16 / sizeof(REAL);
+    return (a->nx % 2 == 0) && (a->pitch % vec == 0) && a->nx >= 8 && ((uintptr_t)u_in % 16 == 0) && ((uintptr_t)u_out % 16 == 0) &&
+           (a->stage == 1 || (uintptr_t)uo % 16 == 0) && get_tmap_encode() != nullptr;
+}
+
+template <typename REAL>
+static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st, PeerOut peer = kNoPeer)
 {
     int rc = check_stage_args(a, u_in, uo, u_out, 5);
     if (rc) return rc;
@@ -218,12 +231,11 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     HeatArgs<REAL> h;
     rc = heat_args_from<REAL>(a, h);
     if (rc) return rc;
+    h.out2 = (REAL*)peer.out2; h.off2 = peer.off2;
     // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
     static const int heat_variant = getenv("ADV_HEAT_VARIANT") ? atoi(getenv("ADV_HEAT_VARIANT")) : 10;
-    const size_t vec = 16 / sizeof(REAL);
-    const bool tma_ok = heat_variant > 0 && (a->nx % 2 == 0) && (a->pitch % vec == 0) && a->nx >= 8 &&
-                        ((uintptr_t)u_in % 16 == 0) && ((uintptr_t)u_out % 16 == 0) && (a->stage == 1 || (uintptr_t)uo % 16 == 0) &&
-                        get_tmap_encode() != nullptr;
+    const bool tma_ok = heat_variant > 0 && heat3d_tma_ok<REAL>(a, u_in, uo, u_out);
+    if (peer.out2 && !(tma_ok && heat_variant == 10)) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
     if (tma_ok) {
         if (heat_variant == 10) return heat3d_launch_tma2<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
         if (heat_variant == 11) return heat3d_launch_tma2<REAL, 8, 8>(a, h, u_in, uo, u_out, st);
@@ -260,7 +272,7 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
 }
 
 template <typename REAL>
-static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, REAL* rowacc, cudaStream_t st)
+static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, REAL* rowacc, cudaStream_t st, PeerOut peer = kNoPeer)
 {
     int rc = check_stage_args(a, u_in, uo, u_out, 7);
     if (rc) return rc;
@@ -279,6 +291,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     b.dt = (REAL)a->dt; b.dx = (REAL)a->dx; b.dy = (REAL)a->dy; b.dz = (REAL)a->dz;
     b.rdx = REAL(1) / b.dx; b.rdy = REAL(1) / b.dy; b.rdz = REAL(1) / b.dz;
     b.kx = (REAL)a->kx; b.ky = (REAL)a->ky; b.kz = (REAL)a->kz;
+    b.out2 = (REAL*)peer.out2; b.off2 = peer.off2;
     b.visc = (!mg && (a->kx != 0 || a->ky != 0 || a->kz != 0)) ? 1 : 0;
     b.quirk_lo = 1; b.quirk_hi = 0;
     if (!mg && !(a->flags & ADV_FLAG_VISC_ONCE)) { b.quirk_lo = 16 - a->k_global0; b.quirk_hi = 18 - a->k_global0; }
@@ -289,6 +302,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
     static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 32;
+    if (peer.out2 && (force_direct || ring < 30)) return fail(ADV_ERR_INVALID, "fused halo stores need the ring4 Burgers kernel");
     if (!force_direct && ring >= 30) {
         // v6: specialised split-barrier ring kernel.  30: 32x8 CPT1 3 CTAs/SM; 32 (default): 32x16 CPT2 2 CTAs/SM;
         // 33: 32x14 CPT2 (256 threads, 128 registers)
@@ -432,6 +446,14 @@ struct adv_solver {
     void* buf[3];               // ping-pong field buffers; buf[cur] holds the solution
     int cur;
     void* rowacc;               // Burgers MGPU scratch (pitch * nzs)
+    // one device allocation ("arena") holds the three buffers, the scratch and the halo flags, so that a
+    // neighbour rank can map all of it with a single IPC handle and address it by the same offsets
+    char* arena;
+    size_t arena_bytes, off_buf[3], off_rowacc, off_flags;
+    char* peer_base[2];         // [0] left, [1] right neighbour's arena as seen from this device
+    bool peer_is_ipc[2];
+    int p2p;                    // 1: halo planes are stored straight into the neighbours' ghost planes
+    unsigned stage_counter;     // stages executed so far (the value the halo flags carry)
     cudaStream_t stream, comm_stream;
     cudaEvent_t ev_start, ev_stop, ev_boundary, ev_comm;
     bool uploaded;
@@ -542,10 +564,21 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
 #define CREATE_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { \
         int _c = fail(_e == cudaErrorMemoryAllocation ? ADV_ERR_NOMEM : ADV_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e)); \
         adv_destroy(s); return _c; } } while (0)
-    for (int b = 0; b < 3; b++) CREATE_TRY(cudaMalloc(&s->buf[b], s->buf_bytes));
-    if (desc->target == ADV_TARGET_BURGERS3D_MGPU) {
-        CREATE_TRY(cudaMalloc(&s->rowacc, s->pitch * (size_t)s->nzs * s->esz));
-        CREATE_TRY(cudaMemset(s->rowacc, 0, s->pitch * (size_t)s->nzs * s->esz));
+    {
+        const size_t al = 512;
+        size_t off = 0;
+        const size_t bufb = (s->buf_bytes + al - 1) / al * al;
+        for (int b = 0; b < 3; b++) { s->off_buf[b] = off; off += bufb; }
+        s->off_rowacc = off;
+        const size_t accb = desc->target == ADV_TARGET_BURGERS3D_MGPU ? (s->pitch * (size_t)s->nzs * s->esz + al - 1) / al * al : 0;
+        off += accb;
+        s->off_flags = off;
+        off += al;
+        s->arena_bytes = off;
+        CREATE_TRY(cudaMalloc((void**)&s->arena, s->arena_bytes));
+        for (int b = 0; b < 3; b++) s->buf[b] = s->arena + s->off_buf[b];
+        if (accb) s->rowacc = s->arena + s->off_rowacc;
+        CREATE_TRY(cudaMemset(s->arena + s->off_rowacc, 0, accb + al));
     }
     CREATE_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CREATE_TRY(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
@@ -569,8 +602,8 @@ extern "C" int adv_destroy(adv_solver* s)
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
     s->comm.destroy();
-    for (int b = 0; b < 3; b++) if (s->buf[b]) cudaFree(s->buf[b]);
-    if (s->rowacc) cudaFree(s->rowacc);
+    for (int n = 0; n < 2; n++) if (s->peer_base[n] && s->peer_is_ipc[n]) cudaIpcCloseMemHandle(s->peer_base[n]);
+    if (s->arena) cudaFree(s->arena);
     if (s->ev_start) cudaEventDestroy(s->ev_start);
     if (s->ev_stop) cudaEventDestroy(s->ev_stop);
     if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);
@@ -700,7 +733,8 @@ extern "C" int adv_init_reference_ic(adv_solver* s)
 // With ranks > 1 each stage computes the two 3-plane boundary slabs first, hands them to the
 // halo exchange on the comm stream, and computes the interior while they travel.
 // ------------------------------------------------------------------------------------------
-static int launch_stage(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke, cudaStream_t st)
+static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke,
+                             cudaStream_t st, PeerOut peer)
 {
     if (kb >= ke) return ADV_OK;
     adv_stage_args a;
@@ -721,19 +755,112 @@ static int launch_stage(adv_solver* s, int stage, double dt, const void* in, con
         break;
     case ADV_TARGET_BURGERS3D_SGPU:
     case ADV_TARGET_BURGERS3D_MGPU:
-        rc = f64 ? adv_burgers3d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, (double*)s->rowacc, st)
-                 : adv_burgers3d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, (float*)s->rowacc, st);
+        rc = f64 ? burgers3d_stage_impl<double>(&a, (const double*)in, (const double*)uo, (double*)out, (double*)s->rowacc, st, peer)
+                 : burgers3d_stage_impl<float>(&a, (const float*)in, (const float*)uo, (float*)out, (float*)s->rowacc, st, peer);
         break;
     default:
-        rc = f64 ? adv_heat3d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, st)
-                 : adv_heat3d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, st);
+        rc = f64 ? heat3d_stage_impl<double>(&a, (const double*)in, (const double*)uo, (double*)out, st, peer)
+                 : heat3d_stage_impl<float>(&a, (const float*)in, (const float*)uo, (float*)out, st, peer);
     }
     if (!rc) s->launches++;
     return rc;
 }
 
+static int launch_stage(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke, cudaStream_t st)
+{
+    return launch_stage_peer(s, stage, dt, in, uo, out, kb, ke, st, kNoPeer);
+}
+
+// ---- fused halo exchange over peer memory --------------------------------------------------------
+// flag words inside every arena: [0] written by the left neighbour, [32] by the right one (128 B apart)
+enum { FLAG_FROM_LEFT = 0, FLAG_FROM_RIGHT = 32 };
+
+__global__ void halo_signal_kernel(volatile unsigned* flag, unsigned value)
+{
+    __threadfence_system();         // the boundary-slab kernel before us in the stream has completed its peer stores
+    *flag = value;
+    __threadfence_system();
+}
+__global__ void halo_wait_kernel(const volatile unsigned* flag, unsigned value)
+{
+    while ((int)(*flag - value) < 0) __nanosleep(200);
+}
+
+typedef CUresult (*stream_wait32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static stream_wait32_fn get_stream_wait32()
+{
+    static stream_wait32_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (!getenv("ADV_HALO_SPIN_WAIT") &&
+            cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (stream_wait32_fn)p;
+    }
+    return fn;
+}
+
+static int halo_wait(adv_solver* s, int which, unsigned value)
+{
+    unsigned* flag = (unsigned*)(s->arena + s->off_flags) + which;
+    stream_wait32_fn w = get_stream_wait32();
+    if (w) {
+        CUresult r = w((CUstream)s->stream, (CUdeviceptr)flag, value, 0 /* CU_STREAM_WAIT_VALUE_GEQ */);
+        if (r == CUDA_SUCCESS) return ADV_OK;
+    }
+    halo_wait_kernel<<<1, 1, 0, s->stream>>>(flag, value);
+    CUDA_TRY(cudaGetLastError());
+    s->launches++;
+    return ADV_OK;
+}
+
+static int halo_signal(adv_solver* s, int nbr, int which, unsigned value)
+{
+    unsigned* flag = (unsigned*)(s->peer_base[nbr] + s->off_flags) + which;
+    halo_signal_kernel<<<1, 1, 0, s->stream>>>(flag, value);
+    CUDA_TRY(cudaGetLastError());
+    s->launches++;
+    return ADV_OK;
+}
+
+static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke,
+                             cudaStream_t st, PeerOut peer);
+
+// One stage with the exchange fused into the boundary-slab kernels: they store their three planes both
+// locally and, through NVLink peer mappings, into the neighbour's ghost planes; a flag per neighbour
+// says "stage c has landed".  A rank starts stage c once both neighbours have signalled c-1, which is
+// also when they have stopped reading the ghost planes this stage overwrites.  No NCCL, no comm stream.
+static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out)
+{
+    const int P = s->d.nranks, r = s->d.rank, R = ADV_RADIUS;
+    const unsigned c = ++s->stage_counter;
+    int ob = -1;
+    for (int b = 0; b < 3; b++) if (s->buf[b] == out) ob = b;
+    if (ob < 0) return fail(ADV_ERR_STATE, "stage output is not one of the solver's buffers");
+    const long long plane = (long long)s->pitch * s->d.ny;
+    int rc;
+    if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1))) return rc;
+    if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1))) return rc;
+    if (r > 0) {            // my planes [3,6) are the left neighbour's ghost planes [nzs-3, nzs)
+        PeerOut po = {s->peer_base[0] + s->off_buf[ob], (long long)(s->nzs - 2 * R) * plane};
+        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, R, 2 * R, s->stream, po))) return rc;
+    }
+    if (r < P - 1) {        // my planes [nzs-6, nzs-3) are the right neighbour's ghost planes [0, 3)
+        PeerOut po = {s->peer_base[1] + s->off_buf[ob], -(long long)(s->nzs - 2 * R) * plane};
+        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, s->nzs - 2 * R, s->nzs - R, s->stream, po))) return rc;
+    }
+    if (r > 0 && (rc = halo_signal(s, 0, FLAG_FROM_RIGHT, c))) return rc;
+    if (r < P - 1 && (rc = halo_signal(s, 1, FLAG_FROM_LEFT, c))) return rc;
+    const int ilo = (r > 0) ? 2 * R : 0;
+    const int ihi = (r < P - 1) ? s->nzs - 2 * R : s->nzs;
+    return launch_stage_peer(s, stage, dt, in, uo, out, ilo, ihi, s->stream, kNoPeer);
+}
+
 static int do_stage(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out)
 {
+    if (s->d.nranks > 1 && s->p2p) return do_stage_p2p(s, stage, dt, in, uo, out);
     const int P = s->d.nranks, r = s->d.rank;
     if (P == 1) return launch_stage(s, stage, dt, in, uo, out, 0, s->nzs, s->stream);
 
@@ -934,4 +1061,82 @@ extern "C" int adv_burgers3d_stage_f64_noalloc(const adv_stage_args* a, const do
                                  a->pitch * (size_t)(a->k_end - a->k_begin) * sizeof(double), st));
     }
     return burgers3d_stage_impl<double>(a, u_in, uo, u_out, scratch, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// peer (NVLink) halo exchange set-up
+// ------------------------------------------------------------------------------------------
+static int peer_supported(adv_solver* s)
+{
+    if (s->d.nranks < 2) return fail(ADV_ERR_INVALID, "peer halo exchange needs nranks > 1");
+    if (s->d.target == ADV_TARGET_HEAT3D_MGPU) {
+        const size_t vec = 16 / s->esz;
+        if (s->d.nx % 2 || s->pitch % vec || !get_tmap_encode())
+            return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx)");
+    }
+    return ADV_OK;
+}
+
+extern "C" int adv_peer_handle(adv_solver* s, unsigned char handle[64])
+{
+    if (!s || !handle) return fail(ADV_ERR_INVALID, "NULL argument");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, s->arena));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle, &h, 64);
+    return ADV_OK;
+}
+
+extern "C" int adv_peer_connect(adv_solver* s, const unsigned char* left_handle, const unsigned char* right_handle)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    int rc = peer_supported(s);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    const unsigned char* hs[2] = {left_handle, right_handle};
+    const bool need[2] = {s->d.rank > 0, s->d.rank < s->d.nranks - 1};
+    for (int n = 0; n < 2; n++) {
+        if (!need[n]) continue;
+        if (!hs[n]) return fail(ADV_ERR_INVALID, "rank %d needs its %s neighbour's handle", s->d.rank, n ? "right" : "left");
+        cudaIpcMemHandle_t h;
+        memcpy(&h, hs[n], 64);
+        void* p = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        s->peer_base[n] = (char*)p;
+        s->peer_is_ipc[n] = true;
+    }
+    s->p2p = 1;
+    return ADV_OK;
+}
+
+extern "C" int adv_peer_connect_local(adv_solver* s, adv_solver* left, adv_solver* right)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    int rc = peer_supported(s);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    adv_solver* nb[2] = {left, right};
+    const bool need[2] = {s->d.rank > 0, s->d.rank < s->d.nranks - 1};
+    for (int n = 0; n < 2; n++) {
+        if (!need[n]) continue;
+        if (!nb[n]) return fail(ADV_ERR_INVALID, "rank %d needs its %s neighbour", s->d.rank, n ? "right" : "left");
+        if (nb[n]->arena_bytes != s->arena_bytes) return fail(ADV_ERR_INVALID, "neighbour slab has a different layout");
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, s->d.device, nb[n]->d.device));
+        if (!can) return fail(ADV_ERR_CUDA, "device %d cannot access device %d", s->d.device, nb[n]->d.device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(nb[n]->d.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(ADV_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        s->peer_base[n] = nb[n]->arena;
+        s->peer_is_ipc[n] = false;
+    }
+    s->p2p = 1;
+    return ADV_OK;
+}
+
+extern "C" int adv_halo_mode(const adv_solver* s)
+{
+    if (!s || s->d.nranks < 2) return 0;
+    return s->p2p ? 2 : 1;
 }

@@ -1391,7 +1391,11 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                         }
                         const bool rk = (MODE == BMODE_MGPU) ? true : own_m;
                         const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
-                        *pout[c] = rk ? res : u_m[c];
+                        {
+                            const REAL val = rk ? res : u_m[c];
+                            *pout[c] = val;
+                            if (a.out2) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
+                        }
                         Fz_prev[c] = Fz[c];
                     }
                 } else {
@@ -1430,7 +1434,11 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                                 }
                             }
                             const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
-                            *pout[c] = rk ? res : u_m[c];
+                            {
+                            const REAL val = rk ? res : u_m[c];
+                            *pout[c] = val;
+                            if (a.out2) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
+                        }
                         }
                         Fz_prev[c] = Fz[c];
                     }

@@ -35,6 +35,10 @@ struct HeatArgs {
     int iso;                  // 1: kx/12 * (sum - 90 c)  (MultiGPU/Diffusion3d_Baseline/Kernels.cu:240-243)
     int stage;
     REAL kx, ky, kz, dt;
+    // fused halo exchange: when non-null every produced plane is ALSO stored to out2 + off2 (a neighbour
+    // GPU's ghost planes, mapped through NVLink peer access); off2 is an element offset
+    REAL* out2;
+    long long off2;
 };
 
 enum { WENO_JS = 0, WENO_Z = 1 };
@@ -52,6 +56,8 @@ struct BurgersArgs {
     REAL dt, rdx, rdy, rdz;   // spacings passed as given (division kept as in the reference)
     REAL dx, dy, dz;
     REAL kx, ky, kz;
+    REAL* out2;               // fused halo exchange: second destination of every produced plane (peer ghost planes)
+    long long off2;
     // WENO constants read straight from the kernel-parameter constant bank (no immediate moves):
     // [0..2] r_k*13/12, [3..5] r_k/4, [6..8] r_k*eps with r_k = 1/sqrt(d_k) (JS) or 1 (Z);
     // [9] 2/6 [10] 7/6 [11] 11/6 [12] 1/6 [13] 5/6 [14] 0.75 [15] 0.25 [16..18] d_k = .1 .6 .3 [19] 1/3

@@ -392,6 +392,7 @@ heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                     res.y = rk_combine_fast<REAL, STAGE>(zc.y, qo.y, Lu.y, a.dt);
                 }
                 *reinterpret_cast<V2*>(po) = res;
+                if (a.out2) *reinterpret_cast<V2*>(a.out2 + (po - out) + a.off2) = res;
             } else {
                 if (yr && zr) {
                     V2 Lu;
@@ -406,7 +407,10 @@ heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constan
                     res.x = xr0 ? r0 : zc.x;
                     res.y = xr1 ? r1 : zc.y;
                 }
-                if (in_dom) *reinterpret_cast<V2*>(po) = res;
+                if (in_dom) {
+                    *reinterpret_cast<V2*>(po) = res;
+                    if (a.out2) *reinterpret_cast<V2*>(a.out2 + (po - out) + a.off2) = res;
+                }
             }
         }
         if (n >= 2) {

@@ -87,6 +87,19 @@ class Solver:
     def init_reference_ic(self):
         check(lib().adv_init_reference_ic(self._h))
 
+    # -- fused NVLink halo exchange (ranks = processes): exchange the 64-byte handles any way you like
+    def peer_handle(self):
+        h = (C.c_ubyte * 64)()
+        check(lib().adv_peer_handle(self._h, C.byref(h)))
+        return bytes(h)
+
+    def peer_connect(self, left_handle, right_handle):
+        check(lib().adv_peer_connect(self._h, left_handle, right_handle))
+
+    @property
+    def halo_mode(self):
+        return {0: "none", 1: "nccl", 2: "peer"}[lib().adv_halo_mode(self._h)]
+
     # -- time stepping
     def step(self, nsteps=1):
         check(lib().adv_step(self._h, nsteps))

@@ -84,7 +84,7 @@ def run_cpu(rank, P, nx, ny, nz, nsteps):
         print("MP_OK cpu P=%d bit-exact vs oracle" % P)
 
 
-def run_gpu(rank, P, target, nx, ny, nz, nsteps):
+def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
     import multigpu_advectiondiffusion_b200 as adv
     torch.cuda.set_device(rank)
     idb = [None]
@@ -97,6 +97,11 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps):
     g = orc.ic_burgers3d_mgpu(nx, ny, nz) if "burgers" in target else orc.ic_heat3d_mgpu(nx, ny, nz)
     g0, g1 = slab_bounds(nz, P, rank)
     with adv.Solver(target, nx, ny, nz, coef=coef, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
+        if halo == "peer":
+            hs = [None] * P
+            dist.all_gather_object(hs, s.peer_handle())
+            s.peer_connect(hs[rank - 1] if rank > 0 else None, hs[rank + 1] if rank < P - 1 else None)
+        assert s.halo_mode == halo, s.halo_mode
         # the library's own IC slicing must equal Init_subdomain of the reference IC
         s.init_reference_ic()
         assert np.array_equal(s.download(), g[g0:g1]), "rank %d: IC slab differs" % rank
@@ -122,7 +127,7 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps):
             want, _ = orc.heat3d(g, nsteps, "mgpu", L=2.0, W=2.0, H=2.0)
         err = orc.rel_err(merged, want)
         assert err <= 1e-12, err
-        print("MP_OK gpu %s P=%d bit-exact vs P=1, rel err vs oracle %.2e" % (target, P, err))
+        print("MP_OK gpu %s P=%d halo=%s bit-exact vs P=1, rel err vs oracle %.2e" % (target, P, halo, err))
 
 
 def main():
@@ -134,8 +139,9 @@ def main():
         if mode == "cpu":
             run_cpu(rank, P, 20, 22, 24, 2)
         else:
-            for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5)):
-                run_gpu(rank, P, target, *shape, steps)
+            for halo in ("nccl", "peer"):
+                for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5)):
+                    run_gpu(rank, P, target, *shape, steps, halo=halo)
     finally:
         dist.barrier()
         dist.destroy_process_group()

@@ -34,4 +34,4 @@ def test_gpu_nccl_two_ranks():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
     r = _launch("gpu", 2, 29733)
-    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 2, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 4 and r.stdout.count("halo=peer") == 2, r.stdout[-3000:] + r.stderr[-3000:]
