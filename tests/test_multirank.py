@@ -35,3 +35,13 @@ def test_gpu_nccl_two_ranks():
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
     r = _launch("gpu", 2, 29733)
     assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 4 and r.stdout.count("halo=peer") == 2, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.gpu
+def test_gpu_four_ranks_both_halo_modes():
+    """Ranks with two neighbours (P=4): NCCL and fused-peer halo paths, bit-exact against P=1."""
+    import torch
+    if torch.cuda.device_count() < 4:
+        pytest.skip("needs 4 GPUs (run under gpurun --gpus 4)")
+    r = _launch("gpu", 4, 29734)
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 4 and r.stdout.count("halo=peer") == 2, r.stdout[-3000:] + r.stderr[-3000:]
