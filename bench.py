@@ -37,6 +37,7 @@ WORKLOADS = {
     "heat3d_256": dict(target="heat3d_mgpu", n=(256, 256, 256), scaling="weak", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=100),
     "heat3d_weak512": dict(target="heat3d_mgpu", n=(512, 512, 512), scaling="weak", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
     "heat3d_strong1024": dict(target="heat3d_mgpu", n=(1024, 1024, 1024), scaling="strong", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
+    "heat2d_512": dict(target="heat2d_sgpu", n=(512, 512, 1), scaling="replicas", L=(10, 10, 1), coef=1.0, e2e_steps=1000),
     "heat3d_sgpu_256": dict(target="heat3d_sgpu_baseline", n=(256, 256, 256), scaling="replicas", L=(10, 10, 10), coef=1.0, e2e_steps=100),
 }
 BYTES_PER_CELL_STEP = {8: 64.0, 4: 32.0}     # 16 + 24 + 24, per time step
@@ -143,6 +144,14 @@ def cpu_sample(w, precision_bytes, target_seconds=12.0):
             f(u.ctypes.data, uo.ctypes.data, Lu.ctypes.data, nx, ny, planes, 1.0, 1.0, 1.0, 1e-6, 2)
         return time.perf_counter() - t0
 
+    if w["target"] == "heat2d_sgpu":
+        u0 = orc.ic_heat2d_sgpu(nx, ny)
+        steps = 300
+        t0 = time.perf_counter()
+        orc.heat2d(u0, steps)
+        t = time.perf_counter() - t0
+        return {"value": nx * ny * 3 * steps / t / 1e6, "unit": "Mcell-updates/s", "cores": threads, "kind": "port",
+                "sample": "%dx%d, %d time steps, oracle/advdiff_oracle.c with OpenMP" % (nx, ny, steps), "seconds": t}
     planes = 14
     t = run(planes, 1)                                  # calibration (also warms the pages)
     rate = nx * ny * planes * 3 / t
@@ -233,6 +242,8 @@ def main():
         dist.broadcast(idt, 0)
         comm_id = bytes(idt.cpu().tolist())
 
+    if w["target"] == "heat2d_sgpu":
+        config["l2_policy"] = "L2-resident by nature: 3 x 2 MiB field (launch-latency bound, SURVEY 8a2)"
     s = adv.Solver(w["target"], nx, ny, nz_total, lx=w["L"][0], ly=w["L"][1], lz=lz, coef=w["coef"],
                    precision=adv.F64 if esz == 8 else adv.F32, device=dev, nranks=nranks, rank=rank if nranks > 1 else 0,
                    comm_id=comm_id)

@@ -315,11 +315,15 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         const int chunk = (planes + nch - 1) / nch;
         dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
-#define LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, STAGE_) do { \
-            auto kfn = burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_>; \
+#define LAUNCH_RING4_P(W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_) do { \
+            auto kfn = burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_>; \
             const size_t shm = sizeof(BurgersRing4Smem<REAL, TY_>); \
             CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
             kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
+#define LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, STAGE_) do { \
+            if (b.out2) { if (M_ == BMODE_MGPU && TY_ == 16) LAUNCH_RING4_P(W_, BMODE_MGPU, 16, 2, 2, STAGE_, true); \
+                          else return fail(ADV_ERR_INVALID, "fused halo stores need the default ring kernel"); } \
+            else LAUNCH_RING4_P(W_, M_, TY_, CPT_, MINB_, STAGE_, false); } while (0)
 #define LAUNCH_RING4_S(W_, M_, TY_, CPT_, MINB_) do { \
             if (a->stage == 1) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 1); \
             else if (a->stage == 2) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 2); \
@@ -330,6 +334,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         else LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 16, 2, 2);
 #undef LAUNCH_RING4_S
 #undef LAUNCH_RING4
+#undef LAUNCH_RING4_P
     } else if (mg && !force_direct && ring >= 20) {
         // v5: split-barrier ring kernel.  20: 32x8 CPT1 3 CTAs/SM; 21: 32x8 CPT2; 22: 32x16 CPT2 2 CTAs/SM
         const int TYv = (ring >= 22) ? 16 : 8;
@@ -454,6 +459,10 @@ struct adv_solver {
     bool peer_is_ipc[2];
     int p2p;                    // 1: halo planes are stored straight into the neighbours' ghost planes
     unsigned stage_counter;     // stages executed so far (the value the halo flags carry)
+    // small single-rank problems are launch-bound: three time steps (one full rotation of the three
+    // buffers, nine stage launches) are captured once into a CUDA graph and replayed
+    cudaGraphExec_t graph_exec;
+    int graph_cur;              // value of `cur` the captured graph starts from
     cudaStream_t stream, comm_stream;
     cudaEvent_t ev_start, ev_stop, ev_boundary, ev_comm;
     bool uploaded;
@@ -602,6 +611,7 @@ extern "C" int adv_destroy(adv_solver* s)
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->comm_stream) cudaStreamSynchronize(s->comm_stream);
     s->comm.destroy();
+    if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     for (int n = 0; n < 2; n++) if (s->peer_base[n] && s->peer_is_ipc[n]) cudaIpcCloseMemHandle(s->peer_base[n]);
     if (s->arena) cudaFree(s->arena);
     if (s->ev_start) cudaEventDestroy(s->ev_start);
@@ -904,8 +914,34 @@ extern "C" int adv_step(adv_solver* s, int nsteps)
     if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_step before adv_upload");
     if (nsteps < 0) return fail(ADV_ERR_INVALID, "nsteps < 0");
     CUDA_TRY(cudaSetDevice(s->d.device));
+    static const bool no_graph = getenv("ADV_NO_GRAPH") != nullptr;
+    const size_t cells = (size_t)s->d.nx * s->d.ny * s->nzs;
+    const bool use_graph = !no_graph && s->d.nranks == 1 && nsteps >= 12 && cells <= ((size_t)1 << 23);
+    if (use_graph && !s->graph_exec) {
+        // capture three steps starting from the current buffer assignment
+        cudaGraph_t g = nullptr;
+        const long long l0 = s->launches;
+        const int cur0 = s->cur;
+        CUDA_TRY(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = ADV_OK;
+        for (int n = 0; n < 3 && !rc; n++) rc = do_step(s, s->dt_fixed);
+        cudaError_t e = cudaStreamEndCapture(s->stream, &g);
+        s->launches = l0;
+        s->cur = cur0;
+        if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+        if (e != cudaSuccess) return fail(ADV_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&s->graph_exec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { s->graph_exec = nullptr; return fail(ADV_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e)); }
+        s->graph_cur = cur0;
+    }
     CUDA_TRY(cudaEventRecord(s->ev_start, s->stream));
-    for (int n = 0; n < nsteps; n++) {
+    int n = 0;
+    if (use_graph) {
+        while (n < nsteps && s->cur != s->graph_cur) { int rc = do_step(s, s->dt_fixed); if (rc) return rc; n++; }
+        for (; n + 3 <= nsteps; n += 3) { CUDA_TRY(cudaGraphLaunch(s->graph_exec, s->stream)); s->launches += 9; }
+    }
+    for (; n < nsteps; n++) {
         int rc = do_step(s, s->dt_fixed);
         if (rc) return rc;
     }

@@ -1229,7 +1229,7 @@ __device__ __forceinline__ REAL rk_stage(REAL u_m, REAL uo_m, REAL Lu, REAL dt, 
     return (uo_m + REAL(2) * t) * wc[19];
 }
 
-template <typename REAL, int W, int MODE, int TY, int CPT, int MINB, int STAGE>
+template <typename REAL, int W, int MODE, int TY, int CPT, int MINB, int STAGE, bool PEER>
 __global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
 burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
                       REAL* __restrict__ out, REAL* __restrict__ rowacc)
@@ -1394,7 +1394,7 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                         {
                             const REAL val = rk ? res : u_m[c];
                             *pout[c] = val;
-                            if (a.out2) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
+                            if (PEER) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
                         }
                         Fz_prev[c] = Fz[c];
                     }
@@ -1437,7 +1437,7 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                             {
                             const REAL val = rk ? res : u_m[c];
                             *pout[c] = val;
-                            if (a.out2) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
+                            if (PEER) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
                         }
                         }
                         Fz_prev[c] = Fz[c];
