@@ -301,12 +301,12 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
     static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
-    static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 32;
+    static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 42;
     if (peer.out2 && (force_direct || ring < 30)) return fail(ADV_ERR_INVALID, "fused halo stores need the ring4 Burgers kernel");
     if (!force_direct && ring >= 30) {
         // v6: specialised split-barrier ring kernel.  30: 32x8 CPT1 3 CTAs/SM; 32 (default): 32x16 CPT2 2 CTAs/SM;
         // 33: 32x14 CPT2 (256 threads, 128 registers)
-        const int TYv = !mg ? 16 : (ring == 33) ? 14 : (ring == 30) ? 8 : 16;
+        const int TYv = !mg ? 16 : (ring == 33 || ring == 43) ? 14 : (ring == 30) ? 8 : 16;
         const int planes = a->k_end - a->k_begin;
         const int gx = (a->nx + 31) / 32, gy = (a->ny + TYv - 1) / TYv;
         int nch = (1776 + gx * gy - 1) / (gx * gy);
@@ -316,7 +316,8 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
 #define LAUNCH_RING4_P(W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_) do { \
-            auto kfn = burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_>; \
+            auto kfn = (ring >= 40) ? burgers3d_stage_ring5<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_> \
+                                    : burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_>; \
             const size_t shm = sizeof(BurgersRing4Smem<REAL, TY_>); \
             CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
             kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
@@ -330,7 +331,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
             else LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 3); } while (0)
         if (!mg) LAUNCH_RING4_S(WENO_Z, BMODE_SGPU, 16, 2, 2);
         else if (ring == 30) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 8, 1, 3);
-        else if (ring == 33) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 14, 2, 2);
+        else if (ring == 33 || ring == 43) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 14, 2, 2);
         else LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 16, 2, 2);
 #undef LAUNCH_RING4_S
 #undef LAUNCH_RING4

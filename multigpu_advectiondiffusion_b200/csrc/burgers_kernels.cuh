@@ -1488,4 +1488,308 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
     }
 }
 
+
+// =============================================================================================
+// v7 ("ring, steady state"): ring4 with the per-plane bookkeeping stripped from the steady state.
+// The kernel is issue-bound -- an FP64 instruction holds the issue port for two cycles, every other
+// instruction for one or more (tools/fp64_mix.cu: one IMAD per DFMA already costs a third of the FP64
+// peak) -- so what is left to gain is the count of non-FP64 instructions:
+//  - compute warps and the edge warp run separate loops (no role tests inside);
+//  - planes whose flags are all "on" in tiles that lie inside the update region run a body compiled
+//    without any of the window / ownership / domain / seed tests (FAST), everything else the general one;
+//  - one running plane offset instead of per-cell pointers; the split's sign test is an integer compare.
+// =============================================================================================
+template <typename REAL> __device__ __forceinline__ bool is_neg(REAL v);
+template <> __device__ __forceinline__ bool is_neg<double>(double v) { return __double2hiint(v) < 0; }
+template <> __device__ __forceinline__ bool is_neg<float>(float v) { return __float_as_int(v) < 0; }
+
+template <bool B> struct BoolTag { static constexpr bool value = B; };
+
+template <typename REAL, int W, int MODE, int TY, int CPT, int MINB, int STAGE, bool PEER>
+__global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
+burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
+                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
+{
+    typedef typename V2T<REAL>::type V2;
+    typedef BurgersRing4Smem<REAL, TY> S;
+    constexpr int TX = S::TX, H = S::H, RP = S::RP, NSLOT = S::NSLOT, NHALO = S::NHALO;
+    constexpr int NW = TY / CPT;
+    constexpr int NT = 32 * (NW + 1);
+    constexpr int NPH = (NHALO + NT - 1) / NT;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    S& sm = *reinterpret_cast<S*>(smem_raw);
+
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int tid = ty * 32 + tx;
+    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+    const int kb = a.kb + blockIdx.z * chunk;
+    const int ke = min(kb + chunk, a.ke);
+    if (kb >= ke) return;
+    const long long P = a.pitch, Z = a.plane;
+    const REAL* __restrict__ wc = a.wc;
+    const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.bar);
+    const bool interior = (i0 >= 3) && (i0 + TX - 1 <= a.nx - 4) && (j0 >= 3) && (j0 + TY - 1 <= a.ny - 4);
+    // steady-state planes: finish m, own m and m+1, stage m+4, read u(m+1) -- all inside the chunk and the slab
+    const int f0 = max(kb, a.own_lo), f1 = min(min(ke - 2, a.own_hi - 2), a.nzs - 5);
+
+    // halo points of the tile staged by this thread
+    int h_idx[NPH];
+    long long h_off[NPH];
+    bool h_ok[NPH];
+#pragma unroll
+    for (int n = 0; n < NPH; n++) {
+        const int hh = tid + n * NT;
+        int r, cc;
+        if (hh < H * RP) { r = hh / RP; cc = hh - r * RP; }
+        else if (hh < 2 * H * RP) { const int t = hh - H * RP; r = t / RP; cc = t - r * RP; r += H + TY; }
+        else { const int t = hh - 2 * H * RP; r = H + t / (2 * H); const int q = t - (t / (2 * H)) * (2 * H); cc = q < H ? q : TX + q; }
+        const int gi = i0 - H + cc, gj = j0 - H + r;
+        h_idx[n] = (hh < NHALO) ? r * RP + cc : -1;
+        h_ok[n] = hh < NHALO && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
+        h_off[n] = h_ok[n] ? (long long)gi + P * gj : 0;
+    }
+    auto split = [&](REAL v) -> V2 {
+        const REAL sq = v * v;
+        const bool ng = is_neg<REAL>(v);
+        V2 r;
+        r.x = (ng ? -wc[15] : wc[14]) * sq;
+        r.y = (ng ? wc[14] : -wc[15]) * sq;
+        return r;
+    };
+    REAL st_halo[NPH];
+    auto fetch_halo = [&](auto fast, int p) {
+        constexpr bool FAST = decltype(fast)::value;
+        const REAL* __restrict__ up = u + Z * p;
+        const bool pl = FAST || (p >= 0 && p < a.nzs);
+#pragma unroll
+        for (int n = 0; n < NPH; n++) {
+            if (FAST) { if ((n + 1) * NT <= NHALO || h_idx[n] >= 0) st_halo[n] = up[h_off[n]]; }
+            else st_halo[n] = (pl && h_ok[n]) ? up[h_off[n]] : REAL(0);
+        }
+    };
+    auto park_halo = [&](int sidx) {
+        V2* __restrict__ sp = sm.slot[sidx];
+#pragma unroll
+        for (int n = 0; n < NPH; n++) if ((n + 1) * NT <= NHALO || h_idx[n] >= 0) sp[h_idx[n]] = split(st_halo[n]);
+    };
+    auto slot_of = [&](int s0, int d) -> int { int t = s0 + d; return t >= NSLOT ? t - NSLOT : t; };
+
+    if (tid == 0) mbar_init(bar, NT);
+
+    if (ty == NW) {
+        // =============================== edge warp ===============================
+        for (int d = 0; d < 6; d++) { fetch_halo(BoolTag<false>(), kb - 3 + d); park_halo(d); }
+        __syncthreads();
+        mbar_arrive(bar);
+        unsigned parity = 0;
+        int s0 = 0;
+        for (int m = kb - 1; m < ke; m++) {
+            const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
+            const bool do_fetch = (m + 4 <= ke + 2);
+            const int nb = (m & 1) ^ 1;
+            if (do_fetch) fetch_halo(BoolTag<false>(), m + 4);
+            mbar_wait_hint(bar, parity);
+            parity ^= 1u;
+            if (do_pairs) {
+                const V2* __restrict__ s3 = sm.slot[slot_of(s0, 3)];
+#pragma unroll 1
+                for (int it = tx; it < 2 * (TX + TY); it += 32) {
+                    int oc, st;
+                    bool minus;
+                    if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
+                    else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
+                    else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
+                    else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
+                    const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
+                    const REAL v = weno_side_d<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
+                                                        minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
+                    if (it < TY) sm.edge_hn_x[nb][it] = v;
+                    else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
+                    else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
+                    else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
+                }
+            }
+            if (do_fetch) park_halo(slot_of(s0, 6));
+            mbar_arrive(bar);
+            s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
+        }
+        return;
+    }
+
+    // =============================== compute warps ===============================
+    const int i = i0 + tx;
+    bool in_dom[CPT];
+    long long col0 = (long long)i + P * (j0 + ty);     // cell c lives at col0 + c*NW*P
+#pragma unroll
+    for (int c = 0; c < CPT; c++) in_dom[c] = i < a.nx && (j0 + ty + c * NW) < a.ny;
+    if (!in_dom[0]) col0 = 0;
+    const int own0 = (ty + H) * RP + tx + H;
+    constexpr int CS = NW * RP;                        // slot offset between a thread's cells
+
+    REAL st_own[CPT];
+    auto fetch_own = [&](auto fast, int p) {
+        constexpr bool FAST = decltype(fast)::value;
+        const REAL* __restrict__ up = u + Z * p + col0;
+        const bool pl = FAST || (p >= 0 && p < a.nzs);
+#pragma unroll
+        for (int c = 0; c < CPT; c++) st_own[c] = (FAST || (pl && in_dom[c])) ? up[(long long)c * NW * P] : REAL(0);
+    };
+    auto park_own = [&](int sidx) {
+        V2* __restrict__ sp = sm.slot[sidx];
+#pragma unroll
+        for (int c = 0; c < CPT; c++) sp[own0 + c * CS] = split(st_own[c]);
+    };
+    auto zface = [&](const V2* p0, const V2* p1, const V2* p2, const V2* p3, const V2* p4, const V2* p5, int own) -> REAL {
+        const V2 v0 = p0[own], v1 = p1[own], v2 = p2[own], v3 = p3[own], v4 = p4[own], v5 = p5[own];
+        return weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
+    };
+    auto visc13 = [&](const REAL* __restrict__ pc, REAL c0) -> REAL {
+        return a.kx * (-pc[-2] + 16 * pc[-1] - 30 * c0 + 16 * pc[1] - pc[2]) +
+               a.ky * (-pc[-2 * P] + 16 * pc[-P] - 30 * c0 + 16 * pc[P] - pc[2 * P]) +
+               a.kz * (-pc[-2 * Z] + 16 * pc[-Z] - 30 * c0 + 16 * pc[Z] - pc[2 * Z]);
+    };
+
+    for (int d = 0; d < 6; d++) {
+        fetch_own(BoolTag<false>(), kb - 3 + d); fetch_halo(BoolTag<false>(), kb - 3 + d);
+        park_own(d); park_halo(d);
+    }
+    __syncthreads();
+    REAL Fz_prev[CPT], X1[CPT], X2[CPT], u_nxt[CPT], uo_nxt[CPT];
+#pragma unroll
+    for (int c = 0; c < CPT; c++) {
+        u_nxt[c] = uo_nxt[c] = X1[c] = X2[c] = REAL(0);
+        Fz_prev[c] = zface(sm.slot[0], sm.slot[1], sm.slot[2], sm.slot[3], sm.slot[4], sm.slot[5], own0 + c * CS);
+    }
+    long long om = col0 + Z * (kb - 2);                // element offset of cell 0 in plane m, bumped per iteration
+    mbar_arrive(bar);
+    unsigned parity = 0;
+    int s0 = 0;
+
+    auto iteration = [&](auto fast, int m) {
+        constexpr bool FAST = decltype(fast)::value;
+        const bool do_final = FAST || (m >= kb);
+        const bool own_m = FAST || (m >= a.own_lo && m < a.own_hi);
+        const bool do_z = FAST || (do_final && (m >= a.own_lo - 1 && m < a.own_hi));
+        const bool do_pairs = FAST || ((m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi));
+        const bool do_fetch = FAST || (m + 4 <= ke + 2);
+        const int eb = m & 1, nb = eb ^ 1;
+        om += Z;
+        if (do_fetch) { fetch_own(fast, m + 4); fetch_halo(fast, m + 4); }
+        REAL u_m[CPT], uo_m[CPT];
+#pragma unroll
+        for (int c = 0; c < CPT; c++) {
+            u_m[c] = u_nxt[c]; uo_m[c] = uo_nxt[c];
+            if (FAST || (in_dom[c] && m + 1 < ke)) {
+                u_nxt[c] = u[om + Z + (long long)c * NW * P];
+                if (STAGE > 1) uo_nxt[c] = uo[om + Z + (long long)c * NW * P];
+            }
+        }
+        REAL Fz[CPT];
+#pragma unroll
+        for (int c = 0; c < CPT; c++) Fz[c] = REAL(0);
+        if (do_z) {
+            const V2 *p0 = sm.slot[slot_of(s0, 0)], *p1 = sm.slot[slot_of(s0, 1)], *p2 = sm.slot[slot_of(s0, 2)],
+                     *p3 = sm.slot[slot_of(s0, 3)], *p4 = sm.slot[slot_of(s0, 4)], *p5 = sm.slot[slot_of(s0, 5)];
+#pragma unroll
+            for (int c = 0; c < CPT; c++) Fz[c] = zface(p0, p1, p2, p3, p4, p5, own0 + c * CS);
+        }
+        mbar_wait_hint(bar, parity);
+        parity ^= 1u;
+
+        if (do_final) {
+#pragma unroll
+            for (int c = 0; c < CPT; c++) {
+                const int r = ty + c * NW;
+                const long long o = om + (long long)c * NW * P;
+                REAL Lu = REAL(0);
+                if (FAST || interior) {
+                    if (own_m) {
+                        const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
+                        const REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
+                        const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
+                        const REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
+                        Lu = -(fu - fu_old) * a.rdx;
+                        Lu -= (gu - gu_old) * a.rdy;
+                        Lu -= (Fz[c] - Fz_prev[c]) * a.rdz;
+                        if (MODE == BMODE_SGPU && a.visc) {
+                            const REAL term = visc13(u + o, u_m[c]);
+                            Lu += term;
+                            if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
+                        }
+                    }
+                    const bool rk = (MODE == BMODE_MGPU) ? true : own_m;
+                    const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
+                    const REAL val = rk ? res : u_m[c];
+                    out[o] = val;
+                    if (PEER) a.out2[o + a.off2] = val;
+                } else {
+                    const int j = j0 + r;
+                    const bool i_in3 = (i >= 3 && i <= a.nx - 4), j_in3 = (j >= 3 && j <= a.ny - 4);
+                    const bool xa = (MODE == BMODE_MGPU) ? (j_in3 && i >= 2 && i <= a.nx - 4) : (i_in3 && j_in3);
+                    const bool ya = (MODE == BMODE_MGPU) ? (i_in3 && j >= 2 && j <= a.ny - 4) : (i_in3 && j_in3);
+                    const bool za = i_in3 && j_in3;
+                    if (own_m) {
+                        const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
+                        REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
+                        fu_old = ((MODE == BMODE_MGPU) && i == 2) ? REAL(0) : fu_old;
+                        const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
+                        REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
+                        gu_old = ((MODE == BMODE_MGPU) && j == 2) ? REAL(0) : gu_old;
+                        Lu = xa ? -(fu - fu_old) * a.rdx : REAL(0);
+                        Lu = ya ? Lu - (gu - gu_old) * a.rdy : Lu;
+                    }
+                    if (in_dom[c]) {
+                        const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && za);
+                        if (own_m) {
+                            if ((MODE == BMODE_MGPU) && j == 2 && ya) {
+                                const long long ra = (long long)i + P * m;
+                                if (STAGE > 1) Lu += rowacc[ra];
+                                rowacc[ra] = Lu;
+                            }
+                            Lu = za ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz : Lu;
+                            if (MODE == BMODE_SGPU && a.visc && za) {
+                                const REAL term = visc13(u + o, u_m[c]);
+                                Lu += term;
+                                if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
+                            }
+                        }
+                        const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
+                        const REAL val = rk ? res : u_m[c];
+                        out[o] = val;
+                        if (PEER) a.out2[o + a.off2] = val;
+                    }
+                }
+                Fz_prev[c] = Fz[c];
+            }
+        }
+        if (do_pairs) {
+            const V2* __restrict__ s3 = sm.slot[slot_of(s0, 3)];
+#pragma unroll
+            for (int c = 0; c < CPT; c++) {
+                const int r = ty + c * NW;
+                const int own = own0 + c * CS;
+                const V2 cc = s3[own];
+                const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
+                const REAL hn_x = weno_side_d<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
+                const REAL hp_x = weno_side_d<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
+                const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
+                sm.hn_y[nb][r + 1][tx] = weno_side_d<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
+                sm.hp_y[nb][r + 1][tx] = weno_side_d<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
+                const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
+                const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
+                X1[c] = (tx == 31) ? hn_x : hn_x + hpR;
+                X2[c] = (tx == 0) ? hp_x : hnL + hp_x;
+            }
+        }
+        if (do_fetch) { const int t = slot_of(s0, 6); park_own(t); park_halo(t); }
+        mbar_arrive(bar);
+        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
+    };
+
+    for (int m = kb - 1; m < ke; m++) {
+        if (interior && m >= f0 && m <= f1) iteration(BoolTag<true>(), m);
+        else iteration(BoolTag<false>(), m);
+    }
+}
+
 }  // namespace adv
