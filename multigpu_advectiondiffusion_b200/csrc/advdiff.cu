@@ -290,6 +290,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     b.stage = a->stage;
     b.dt = (REAL)a->dt; b.dx = (REAL)a->dx; b.dy = (REAL)a->dy; b.dz = (REAL)a->dz;
     b.rdx = REAL(1) / b.dx; b.rdy = REAL(1) / b.dy; b.rdz = REAL(1) / b.dz;
+    b.rdx6 = b.rdx / REAL(6); b.rdy6 = b.rdy / REAL(6); b.rdz6 = b.rdz / REAL(6);
     b.kx = (REAL)a->kx; b.ky = (REAL)a->ky; b.kz = (REAL)a->kz;
     b.out2 = (REAL*)peer.out2; b.off2 = peer.off2;
     b.visc = (!mg && (a->kx != 0 || a->ky != 0 || a->kz != 0)) ? 1 : 0;

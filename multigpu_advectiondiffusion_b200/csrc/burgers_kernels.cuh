@@ -1499,6 +1499,37 @@ burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
 //    without any of the window / ownership / domain / seed tests (FAST), everything else the general one;
 //  - one running plane offset instead of per-cell pointers; the split's sign test is an integer compare.
 // =============================================================================================
+// SIX TIMES the one-sided WENO5 value: 6h = (-b + 5c + 2d) + [2 (t0-t1) n0 + (t1-t2) n2] / (n0+n1+n2).
+// The candidate polynomial then has small-integer coefficients (immediates, no constant loads) and the
+// factor 6 of the denominator disappears; the caller multiplies the flux difference by 1/(6 dx).
+template <typename REAL, int W>
+__device__ __forceinline__ REAL weno_side6(REAL a, REAL b, REAL c, REAL d, REAL e, const REAL* __restrict__ wc)
+{
+    const REAL t0 = (a - 2 * b) + c, s0 = 3 * c + (a - 4 * b);
+    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
+    const REAL t2 = (c - 2 * d) + e, s2 = 3 * c + (e - 4 * d);
+    const REAL q6 = 2 * d + (5 * c - b);
+    const REAL E0 = (wc[0] * t0) * t0 + ((wc[3] * s0) * s0 + wc[6]);
+    const REAL E1 = (wc[1] * t1) * t1 + ((wc[4] * s1) * s1 + wc[7]);
+    const REAL E2 = (wc[2] * t2) * t2 + ((wc[5] * s2) * s2 + wc[8]);
+    const REAL d01 = t0 - t1, d12 = t1 - t2;
+    if (W == WENO_JS) {
+        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
+        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
+        const REAL A = d01 * n0;
+        const REAL num = d12 * n2 + (A + A);
+        return num * fast_rcp((n0 + n1) + n2) + q6;
+    } else {
+        const REAL tau = fabs(E0 - E2);
+        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
+        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
+        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
+        const REAL A = d01 * A0;
+        const REAL num = d12 * A2 + (A + A);
+        return num * fast_rcp((A0 + A1) + A2) + q6;
+    }
+}
+
 template <typename REAL> __device__ __forceinline__ bool is_neg(REAL v);
 template <> __device__ __forceinline__ bool is_neg<double>(double v) { return __double2hiint(v) < 0; }
 template <> __device__ __forceinline__ bool is_neg<float>(float v) { return __float_as_int(v) < 0; }
@@ -1601,7 +1632,7 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                     else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
                     else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
                     const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
-                    const REAL v = weno_side_d<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
+                    const REAL v = weno_side6<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
                                                         minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
                     if (it < TY) sm.edge_hn_x[nb][it] = v;
                     else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
@@ -1641,7 +1672,7 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
     };
     auto zface = [&](const V2* p0, const V2* p1, const V2* p2, const V2* p3, const V2* p4, const V2* p5, int own) -> REAL {
         const V2 v0 = p0[own], v1 = p1[own], v2 = p2[own], v3 = p3[own], v4 = p4[own], v5 = p5[own];
-        return weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
+        return weno_side6<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side6<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
     };
     auto visc13 = [&](const REAL* __restrict__ pc, REAL c0) -> REAL {
         return a.kx * (-pc[-2] + 16 * pc[-1] - 30 * c0 + 16 * pc[1] - pc[2]) +
@@ -1708,9 +1739,9 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                         const REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
                         const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
                         const REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                        Lu = -(fu - fu_old) * a.rdx;
-                        Lu -= (gu - gu_old) * a.rdy;
-                        Lu -= (Fz[c] - Fz_prev[c]) * a.rdz;
+                        Lu = -(fu - fu_old) * a.rdx6;
+                        Lu -= (gu - gu_old) * a.rdy6;
+                        Lu -= (Fz[c] - Fz_prev[c]) * a.rdz6;
                         if (MODE == BMODE_SGPU && a.visc) {
                             const REAL term = visc13(u + o, u_m[c]);
                             Lu += term;
@@ -1735,8 +1766,8 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                         const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
                         REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
                         gu_old = ((MODE == BMODE_MGPU) && j == 2) ? REAL(0) : gu_old;
-                        Lu = xa ? -(fu - fu_old) * a.rdx : REAL(0);
-                        Lu = ya ? Lu - (gu - gu_old) * a.rdy : Lu;
+                        Lu = xa ? -(fu - fu_old) * a.rdx6 : REAL(0);
+                        Lu = ya ? Lu - (gu - gu_old) * a.rdy6 : Lu;
                     }
                     if (in_dom[c]) {
                         const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && za);
@@ -1746,7 +1777,7 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                                 if (STAGE > 1) Lu += rowacc[ra];
                                 rowacc[ra] = Lu;
                             }
-                            Lu = za ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz : Lu;
+                            Lu = za ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz6 : Lu;
                             if (MODE == BMODE_SGPU && a.visc && za) {
                                 const REAL term = visc13(u + o, u_m[c]);
                                 Lu += term;
@@ -1770,11 +1801,11 @@ burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u
                 const int own = own0 + c * CS;
                 const V2 cc = s3[own];
                 const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
-                const REAL hn_x = weno_side_d<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
-                const REAL hp_x = weno_side_d<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
+                const REAL hn_x = weno_side6<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
+                const REAL hp_x = weno_side6<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
                 const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
-                sm.hn_y[nb][r + 1][tx] = weno_side_d<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
-                sm.hp_y[nb][r + 1][tx] = weno_side_d<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
+                sm.hn_y[nb][r + 1][tx] = weno_side6<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
+                sm.hp_y[nb][r + 1][tx] = weno_side6<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
                 const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
                 const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
                 X1[c] = (tx == 31) ? hn_x : hn_x + hpR;

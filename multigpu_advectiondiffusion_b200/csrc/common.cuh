@@ -54,6 +54,7 @@ struct BurgersArgs {
     int visc;                 // SGPU: add kx,ky,kz Laplacian
     int quirk_lo, quirk_hi;   // SGPU: local planes [quirk_lo, quirk_hi] get the viscous term twice (F12); hi<lo: none
     REAL dt, rdx, rdy, rdz;   // spacings passed as given (division kept as in the reference)
+    REAL rdx6, rdy6, rdz6;    // 1/(6 d): the ring5 kernel carries six times the face flux (saves the /6 per side)
     REAL dx, dy, dz;
     REAL kx, ky, kz;
     REAL* out2;               // fused halo exchange: second destination of every produced plane (peer ghost planes)
