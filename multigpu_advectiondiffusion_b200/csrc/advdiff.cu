@@ -137,39 +137,6 @@ static tmap_encode_fn get_tmap_encode()
     return fn;
 }
 
-template <typename REAL, int TY, int NST>
-static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
-{
-    typedef HeatTmaSmem<REAL, TY, NST> S;
-    tmap_encode_fn enc = get_tmap_encode();
-    if (!enc) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    CUtensorMap tm;
-    const cuuint64_t gdim[3] = {(cuuint64_t)a->nx, (cuuint64_t)a->ny, (cuuint64_t)a->nzs};
-    const cuuint64_t gstr[2] = {(cuuint64_t)a->pitch * sizeof(REAL), (cuuint64_t)a->pitch * a->ny * sizeof(REAL)};
-    const cuuint32_t box[3] = {(cuuint32_t)S::BX, (cuuint32_t)S::BY, 1};
-    const cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&tm, sizeof(REAL) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)u_in,
-                     gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(ADV_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
-    const int planes = a->k_end - a->k_begin;
-    const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + TY - 1) / TY;
-    int nch = (2368 + gx * gy - 1) / (gx * gy);             // ~4 waves of 4 CTAs/SM on 148 SMs
-    if (nch > planes / 16) nch = planes / 16;               // 4 planes of z run-in per chunk
-    if (nch < 1) nch = 1;
-    const int chunk = (planes + nch - 1) / nch;
-    dim3 grid(gx, gy, (planes + chunk - 1) / chunk), block(32, TY, 1);
-    const size_t shm = sizeof(S);
-#define HEAT_TMA_LAUNCH(STAGE_) do { \
-        auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_>; \
-        if (shm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-        kfn<<<grid, block, shm, st>>>(tm, h, chunk, uo, u_out); } while (0)
-    if (a->stage == 1) HEAT_TMA_LAUNCH(1); else if (a->stage == 2) HEAT_TMA_LAUNCH(2); else HEAT_TMA_LAUNCH(3);
-#undef HEAT_TMA_LAUNCH
-    CUDA_TRY(cudaGetLastError());
-    return ADV_OK;
-}
-
 static int encode_tmap3(CUtensorMap* tm, int esz, const void* base, int nx, int ny, int nz, size_t pitch, int bx, int by)
 {
     tmap_encode_fn enc = get_tmap_encode();
@@ -186,9 +153,9 @@ static int encode_tmap3(CUtensorMap* tm, int esz, const void* base, int nx, int 
 }
 
 template <typename REAL, int TY, int NST>
-static int heat3d_launch_tma2(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
 {
-    typedef HeatTma2Smem<REAL, TY, NST> S;
+    typedef HeatTmaSmem<REAL, TY, NST> S;
     CUtensorMap tm, tmo;
     int rc = encode_tmap3(&tm, sizeof(REAL), u_in, a->nx, a->ny, a->nzs, a->pitch, S::BX, S::BY);
     if (rc) return rc;
@@ -203,12 +170,12 @@ static int heat3d_launch_tma2(const adv_stage_args* a, const HeatArgs<REAL>& h, 
     const int chunk = (planes + nch - 1) / nch;
     dim3 grid(gx, gy, (planes + chunk - 1) / chunk), block(32, TY + 1, 1);
     const size_t shm = sizeof(S);
-#define HEAT_TMA2_LAUNCH(STAGE_) do { \
-        auto kfn = heat3d_stage_tma2<REAL, TY, NST, STAGE_>; \
+#define HEAT_TMA_LAUNCH(STAGE_) do { \
+        auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_>; \
         if (shm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
         kfn<<<grid, block, shm, st>>>(tm, tmo, h, chunk, u_out); } while (0)
-    if (a->stage == 1) HEAT_TMA2_LAUNCH(1); else if (a->stage == 2) HEAT_TMA2_LAUNCH(2); else HEAT_TMA2_LAUNCH(3);
-#undef HEAT_TMA2_LAUNCH
+    if (a->stage == 1) HEAT_TMA_LAUNCH(1); else if (a->stage == 2) HEAT_TMA_LAUNCH(2); else HEAT_TMA_LAUNCH(3);
+#undef HEAT_TMA_LAUNCH
     CUDA_TRY(cudaGetLastError());
     return ADV_OK;
 }
@@ -233,19 +200,10 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     if (rc) return rc;
     h.out2 = (REAL*)peer.out2; h.off2 = peer.off2;
     // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
-    static const int heat_variant = getenv("ADV_HEAT_VARIANT") ? atoi(getenv("ADV_HEAT_VARIANT")) : 10;
+    static const int heat_variant = getenv("ADV_HEAT_DIRECT") ? 0 : 1;     // A/B switch: ADV_HEAT_DIRECT=1 forces the direct kernel
     const bool tma_ok = heat_variant > 0 && heat3d_tma_ok<REAL>(a, u_in, uo, u_out);
-    if (peer.out2 && !(tma_ok && heat_variant == 10)) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
-    if (tma_ok) {
-        if (heat_variant == 10) return heat3d_launch_tma2<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 11) return heat3d_launch_tma2<REAL, 8, 8>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 12) return heat3d_launch_tma2<REAL, 4, 8>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 13) return heat3d_launch_tma2<REAL, 16, 6>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 2) return heat3d_launch_tma<REAL, 16, 4>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 3) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);
-        if (heat_variant == 4) return heat3d_launch_tma<REAL, 4, 6>(a, h, u_in, uo, u_out, st);
-        return heat3d_launch_tma<REAL, 8, 4>(a, h, u_in, uo, u_out, st);
-    }
+    if (peer.out2 && !tma_ok) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
+    if (tma_ok) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);     // 64x8 tile, 6 planes in flight
     constexpr int CHUNK = 32;
     dim3 block(32, 8, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
@@ -302,123 +260,31 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
     static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
-    static const int ring = getenv("ADV_BURGERS_RING") ? atoi(getenv("ADV_BURGERS_RING")) : 42;
-    if (peer.out2 && (force_direct || ring < 30)) return fail(ADV_ERR_INVALID, "fused halo stores need the ring4 Burgers kernel");
-    if (!force_direct && ring >= 30) {
-        // v6: specialised split-barrier ring kernel.  30: 32x8 CPT1 3 CTAs/SM; 32 (default): 32x16 CPT2 2 CTAs/SM;
-        // 33: 32x14 CPT2 (256 threads, 128 registers)
-        const int TYv = !mg ? 16 : (ring == 33 || ring == 43) ? 14 : (ring == 30) ? 8 : 16;
-        const int planes = a->k_end - a->k_begin;
-        const int gx = (a->nx + 31) / 32, gy = (a->ny + TYv - 1) / TYv;
-        int nch = (1776 + gx * gy - 1) / (gx * gy);
-        if (nch > planes / 16) nch = planes / 16;
-        if (nch < 1) nch = 1;
-        const int chunk = (planes + nch - 1) / nch;
-        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
-        const REAL* uo_ = a->stage == 1 ? u_in : uo;
-#define LAUNCH_RING4_P(W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_) do { \
-            auto kfn = (ring >= 40) ? burgers3d_stage_ring5<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_> \
-                                    : burgers3d_stage_ring4<REAL, W_, M_, TY_, CPT_, MINB_, STAGE_, PEER_>; \
-            const size_t shm = sizeof(BurgersRing4Smem<REAL, TY_>); \
-            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-            kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
-#define LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, STAGE_) do { \
-            if (b.out2) { if (M_ == BMODE_MGPU && TY_ == 16) LAUNCH_RING4_P(W_, BMODE_MGPU, 16, 2, 2, STAGE_, true); \
-                          else return fail(ADV_ERR_INVALID, "fused halo stores need the default ring kernel"); } \
-            else LAUNCH_RING4_P(W_, M_, TY_, CPT_, MINB_, STAGE_, false); } while (0)
-#define LAUNCH_RING4_S(W_, M_, TY_, CPT_, MINB_) do { \
-            if (a->stage == 1) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 1); \
-            else if (a->stage == 2) LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 2); \
-            else LAUNCH_RING4(W_, M_, TY_, CPT_, MINB_, 3); } while (0)
-        if (!mg) LAUNCH_RING4_S(WENO_Z, BMODE_SGPU, 16, 2, 2);
-        else if (ring == 30) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 8, 1, 3);
-        else if (ring == 33 || ring == 43) LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 14, 2, 2);
-        else LAUNCH_RING4_S(WENO_JS, BMODE_MGPU, 16, 2, 2);
-#undef LAUNCH_RING4_S
-#undef LAUNCH_RING4
-#undef LAUNCH_RING4_P
-    } else if (mg && !force_direct && ring >= 20) {
-        // v5: split-barrier ring kernel.  20: 32x8 CPT1 3 CTAs/SM; 21: 32x8 CPT2; 22: 32x16 CPT2 2 CTAs/SM
-        const int TYv = (ring >= 22) ? 16 : 8;
-        const int planes = a->k_end - a->k_begin;
-        const int gx = (a->nx + 31) / 32, gy = (a->ny + TYv - 1) / TYv;
-        int nch = (1776 + gx * gy - 1) / (gx * gy);
-        if (nch > planes / 16) nch = planes / 16;
-        if (nch < 1) nch = 1;
-        const int chunk = (planes + nch - 1) / nch;
-        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
-        const REAL* uo_ = a->stage == 1 ? u_in : uo;
-#define LAUNCH_RING3(TY_, CPT_, MINB_) do { \
-            auto kfn = burgers3d_stage_ring3<REAL, WENO_JS, BMODE_MGPU, TY_, CPT_, MINB_>; \
-            const size_t shm = sizeof(BurgersRing3Smem<REAL, TY_>); \
-            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-            kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
-        if (ring == 20) LAUNCH_RING3(8, 1, 3);
-        else if (ring == 21) LAUNCH_RING3(8, 2, 3);
-        else LAUNCH_RING3(16, 2, 2);
-#undef LAUNCH_RING3
-    } else if (mg && !force_direct && ring >= 10) {
-        // v4: ring kernel with CPT cells per thread.  ring = 10: 32x8 tile CPT 1 (3 CTAs/SM); 11: 32x8 CPT 2 (3 CTAs/SM);
-        // 12: 32x16 CPT 2 (2 CTAs/SM); 13: 32x16 CPT 4 (2 CTAs/SM)
-        const int TYv = (ring >= 12) ? 16 : 8;
-        const int planes = a->k_end - a->k_begin;
-        const int gx = (a->nx + 31) / 32, gy = (a->ny + TYv - 1) / TYv;
-        int nch = (1776 + gx * gy - 1) / (gx * gy);
-        if (nch > planes / 16) nch = planes / 16;
-        if (nch < 1) nch = 1;
-        const int chunk = (planes + nch - 1) / nch;
-        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
-        const REAL* uo_ = a->stage == 1 ? u_in : uo;
-#define LAUNCH_RING2(TY_, CPT_, MINB_) do { \
-            auto kfn = burgers3d_stage_ring2<REAL, WENO_JS, BMODE_MGPU, TY_, CPT_, MINB_>; \
-            const size_t shm = sizeof(BurgersRing2Smem<REAL, TY_>); \
-            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-            kfn<<<tgrid, dim3(32, TY_ / CPT_ + 1, 1), shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
-        if (ring == 10) LAUNCH_RING2(8, 1, 3);
-        else if (ring == 11) LAUNCH_RING2(8, 2, 3);
-        else if (ring == 12) LAUNCH_RING2(16, 2, 2);
-        else LAUNCH_RING2(16, 4, 2);
-#undef LAUNCH_RING2
-    } else if (mg && !force_direct && ring > 0) {
-        // v3 ring kernel: 32x8 tile, 7-slot (f+,f-) plane ring in dynamic shared memory
-        constexpr int TY = 8;
-        typedef BurgersRingSmem<REAL, TY> RS;
+    if (!force_direct) {
+        // ring kernel: 32x16 tile, 2 cells per thread, 8+1 warps, 2 CTAs/SM
+        constexpr int TY = 16, CPT = 2, MINB = 2;
         const int planes = a->k_end - a->k_begin;
         const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
-        int nch = (1776 + gx * gy - 1) / (gx * gy);        // ~4 waves of 3 CTAs/SM
-        if (nch > planes / 16) nch = planes / 16;
+        int nch = (1776 + gx * gy - 1) / (gx * gy);         // ~6 waves of 2 CTAs/SM on 148 SMs ...
+        if (nch > planes / 16) nch = planes / 16;           // ... but chunks of >= 16 planes (6 planes of z run-in each)
         if (nch < 1) nch = 1;
         const int chunk = (planes + nch - 1) / nch;
-        dim3 tblock(32, TY + 1, 1);
-        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
+        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk), tblock(32, TY / CPT + 1, 1);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
-        const size_t shm = sizeof(RS);
-        if (ring == 2) {
-            auto kfn = burgers3d_stage_ring<REAL, WENO_JS, BMODE_MGPU, TY, 2>;
-            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
-            kfn<<<tgrid, tblock, shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
-        } else {
-            auto kfn = burgers3d_stage_ring<REAL, WENO_JS, BMODE_MGPU, TY, 3>;
-            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm));
-            kfn<<<tgrid, tblock, shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
-        }
-    } else if (mg && !force_direct) {
-        // tile variant: 0 = 32x8 tile, 2 CTAs/SM (default); 1 = 32x8, 1 CTA/SM, unconstrained registers; 2 = 32x16 tile
-        static const int variant = getenv("ADV_BURGERS_VARIANT") ? atoi(getenv("ADV_BURGERS_VARIANT")) : 0;
-        const int TY = variant == 2 ? 16 : 8;
-        const int planes = a->k_end - a->k_begin;
-        const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
-        // enough CTAs for ~4 waves of 2 CTAs/SM on 148 SMs, but chunks of at least 16 planes (6 planes of z run-in each)
-        int nch = (1184 + gx * gy - 1) / (gx * gy);
-        if (nch > planes / 16) nch = planes / 16;
-        if (nch < 1) nch = 1;
-        const int chunk = (planes + nch - 1) / nch;
-        dim3 tblock(32, TY + 1, 1);
-        dim3 tgrid(gx, gy, (planes + chunk - 1) / chunk);
-        const REAL* uo_ = a->stage == 1 ? u_in : uo;
-        if (variant == 2)      burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 16, 1><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
-        else if (variant == 1) burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 8, 1><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
-        else                   burgers3d_stage_tiled<REAL, WENO_JS, BMODE_MGPU, 8, 2><<<tgrid, tblock, 0, st>>>(b, chunk, u_in, uo_, u_out, rowacc);
+        const size_t shm = sizeof(BurgersRingSmem<REAL, TY>);
+#define LAUNCH_RING(W_, M_, STAGE_, PEER_) do { \
+            auto kfn = burgers3d_stage_ring<REAL, W_, M_, TY, CPT, MINB, STAGE_, PEER_>; \
+            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
+            kfn<<<tgrid, tblock, shm, st>>>(b, chunk, u_in, uo_, u_out, rowacc); } while (0)
+#define LAUNCH_RING_S(W_, M_, PEER_) do { \
+            if (a->stage == 1) LAUNCH_RING(W_, M_, 1, PEER_); \
+            else if (a->stage == 2) LAUNCH_RING(W_, M_, 2, PEER_); \
+            else LAUNCH_RING(W_, M_, 3, PEER_); } while (0)
+        if (!mg) LAUNCH_RING_S(WENO_Z, BMODE_SGPU, false);
+        else if (b.out2) LAUNCH_RING_S(WENO_JS, BMODE_MGPU, true);
+        else LAUNCH_RING_S(WENO_JS, BMODE_MGPU, false);
+#undef LAUNCH_RING_S
+#undef LAUNCH_RING
     } else if (mg)
         burgers3d_stage_direct<REAL, WENO_JS, BMODE_MGPU, CHUNK><<<grid, block, 0, st>>>(b, u_in, a->stage == 1 ? u_in : uo, u_out, rowacc);
     else

@@ -162,507 +162,38 @@ burgers3d_stage_direct(BurgersArgs<REAL> a, const REAL* __restrict__ u, const RE
 }
 
 // =============================================================================================
-// v2 ("tiled"): every WENO reconstruction is evaluated exactly once.
+// Ring kernel (burgers3d_stage_ring): every WENO reconstruction is evaluated exactly once, and the
+// inner loop is shaped around the issue port (an FP64 instruction holds it for two cycles, everything
+// else for one: tools/fp64_mix.cu).  Development history and measurements: DESIGN.md section 3.2.
 //
-// The face flux f_{c+1/2} = hn(c) + hp(c+1), where hn(c) (minus side, from f+ on c-2..c+2) and
-// hp(c) (plus side of face c-1/2, from f- on c-2..c+2) are both centred on cell c.  Each thread
-// therefore evaluates one (hn,hp) pair per direction for its own cell from ONE 5-point stencil of
-// (f+,f-) and obtains the neighbours' halves through warp shuffles (x), shared memory (y) or its
-// own register queue (z, one plane later).  By symmetry hp(a,b,c,d,e) == hn(e,d,c,b,a), so a single
-// routine serves both sides.  Per z-plane a CTA of TY compute warps (one row of 32 cells each)
-// + 1 "edge" warp (the 2*(32+TY) half reconstructions on the tile rim) works on a 32 x TY tile:
-//   - u of the tile + halo 3 is fetched one plane ahead into registers, converted once to
-//     (f+,f-) and parked in a double-buffered shared-memory slot (LDS.128 gets both);
-//   - z needs no shared memory: 5-deep (f+,f-) register queue, the cell is finished 3 planes
-//     behind the plane being staged.
-// Arithmetic: WENO weights through a common denominator (one division per side instead of the
-// reference's 7), divisions by dx,dy,dz,3 as multiplications by reciprocals, FMA contraction.
-// Same formulas, different rounding: parity is to 1e-12, not bitwise (tests/test_gpu_parity.py).
+//  * Pair formulation.  f_{c+1/2} = hn(c) + hp(c+1): hn(c) (minus side, from f+ on c-2..c+2) and hp(c)
+//    (plus side of face c-1/2, from f- on c-2..c+2) are both centred on cell c, and by symmetry
+//    hp(a,b,c,d,e) == hn(e,d,c,b,a): one routine (weno_side6) serves both.  A thread evaluates one
+//    (hn,hp) pair per direction for each of its cells and gets the neighbours' halves through warp
+//    shuffles (x), shared memory (y) or its own shared-memory column (z).  The 2*(32+TY) halves on
+//    the tile rim are the job of one extra "edge" warp with its own loop.
+//  * (f+,f-) plane ring.  u of tile + halo 3 is fetched one plane ahead, split once
+//    (f+- = {3/4,-1/4} u^2 by sign, exact) and parked as double2 in a 7-slot shared-memory ring; one
+//    LDS.128 returns both.  Iteration m finishes plane m: planes m-2..m+3 are live, m+4 is staged.
+//    The z stencil reads the thread's own column of the ring: only the lower z-face flux and two x
+//    partial sums are loop-carried.
+//  * WENO arithmetic (weno_side6): 6h = (-b+5c+2d) + [2(t0-t1)n0 + (t1-t2)n2] / (n0+n1+n2),
+//    n_k = prod_{m!=k} P_m, P_k = (eps+beta_k)^2/d_k: one reciprocal (rcp.approx + 2 Newton steps)
+//    per side instead of the reference's 7 divisions, ~43 FP64 instructions per side; 1/6 and
+//    1/dx,1/dy,1/dz are folded into one multiplier.  Same formulas, different rounding: parity is to
+//    1e-12, not bitwise (tests/test_gpu_parity.py).
+//  * Split-phase barrier.  One mbarrier per plane: a thread arrives after staging plane m+4 and waits
+//    only after it has computed the z faces of plane m+1, which depend on nothing other threads wrote
+//    (each compute thread stages its own cells; halo points are staged by whoever is free).
+//  * Steady state.  Planes whose window/ownership flags are all on, in tiles inside the update region,
+//    run a body compiled without any of those tests (FAST); rim tiles and the first/last planes of a
+//    chunk run the general body.  RK stage, WENO flavour, target and the peer store are template
+//    parameters; 32x16 tile, 2 cells per thread (rows ty, ty+8), 8+1 warps, 2 CTAs/SM.
 // =============================================================================================
 template <typename REAL> struct V2T;
 template <> struct V2T<double> { typedef double2 type; };
 template <> struct V2T<float> { typedef float2 type; };
 
-__device__ __forceinline__ double fast_div(double num, double den)
-{
-    double y;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(den));      // 2^-23 relative
-    double e = fma(-den, y, 1.0); y = fma(y, e, y);                // 2^-46
-    e = fma(-den, y, 1.0); y = fma(y, e, y);                       // ~2^-52
-    double q = num * y;
-    const double r = fma(-den, q, num);                            // one residual step
-    return fma(r, y, q);
-}
-__device__ __forceinline__ float fast_div(float num, float den) { return __fdividef(num, den); }
-
-// minus-side WENO5 value at the face right of cell c from (a,b,c,d,e) = f[c-2..c+2]
-template <typename REAL, int W>
-__device__ __forceinline__ REAL weno_side(REAL a, REAL b, REAL c, REAL d, REAL e)
-{
-    const REAL t0 = (a - 2 * b) + c, s0 = (a - 4 * b) + 3 * c;
-    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
-    const REAL t2 = (c - 2 * d) + e, s2 = (3 * c - 4 * d) + e;
-    // candidate values already divided by 6
-    const REAL q0 = REAL(2.0 / 6) * a - REAL(7.0 / 6) * b + REAL(11.0 / 6) * c;
-    const REAL q1 = REAL(-1.0 / 6) * b + REAL(5.0 / 6) * c + REAL(2.0 / 6) * d;
-    const REAL q2 = REAL(2.0 / 6) * c + REAL(5.0 / 6) * d - REAL(1.0 / 6) * e;
-    const REAL C1312 = REAL(13.0 / 12.0), C14 = REAL(0.25), EPS = REAL(1e-6);
-    if (W == WENO_JS) {
-        // P_k = (eps+B_k)^2 / d_k  =>  alpha_k = 1/P_k,  w_k = prod_{m!=k} P_m / sum
-        const REAL r0 = REAL(3.1622776601683795), r1 = REAL(1.2909944487358056), r2 = REAL(1.8257418583505538);  // 1/sqrt(.1,.6,.3)
-        REAL E0 = (r0 * C1312 * t0) * t0 + ((r0 * C14 * s0) * s0 + r0 * EPS);
-        REAL E1 = (r1 * C1312 * t1) * t1 + ((r1 * C14 * s1) * s1 + r1 * EPS);
-        REAL E2 = (r2 * C1312 * t2) * t2 + ((r2 * C14 * s2) * s2 + r2 * EPS);
-        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
-        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
-        const REAL den = (n0 + n1) + n2;
-        const REAL num = q0 * n0 + (q1 * n1 + q2 * n2);
-        return fast_div(num, den);
-    } else {
-        // alpha_k = d_k (e_k + tau)/e_k, e_k = B_k + eps;  multiply through by e0 e1 e2
-        const REAL e0 = (C1312 * t0) * t0 + ((C14 * s0) * s0 + EPS);
-        const REAL e1 = (C1312 * t1) * t1 + ((C14 * s1) * s1 + EPS);
-        const REAL e2 = (C1312 * t2) * t2 + ((C14 * s2) * s2 + EPS);
-        const REAL tau = fabs(e0 - e2);
-        const REAL A0 = (REAL(0.1) * (e0 + tau)) * (e1 * e2);
-        const REAL A1 = (REAL(0.6) * (e1 + tau)) * (e0 * e2);
-        const REAL A2 = (REAL(0.3) * (e2 + tau)) * (e0 * e1);
-        const REAL den = (A0 + A1) + A2;
-        const REAL num = q0 * A0 + (q1 * A1 + q2 * A2);
-        return fast_div(num, den);
-    }
-}
-
-template <typename REAL>
-__device__ __forceinline__ typename V2T<REAL>::type lf_split(REAL u)
-{
-    // f+ = 0.5*(0.5 u^2 + |u|u), f- = 0.5*(0.5 u^2 - |u|u): exactly 0.75/-0.25 times u^2 by sign
-    const REAL s = u * u;
-    typename V2T<REAL>::type r;
-    r.x = (u >= 0) ? REAL(0.75) * s : REAL(-0.25) * s;
-    r.y = (u >= 0) ? REAL(-0.25) * s : REAL(0.75) * s;
-    return r;
-}
-
-template <typename REAL, int TY>
-struct BurgersTileSmem {
-    static constexpr int TX = 32, H = 3;
-    static constexpr int RP = TX + 2 * H;              // slot row pitch (points)
-    static constexpr int ROWS = TY + 2 * H;
-    static constexpr int NPTS = RP * ROWS;
-    typename V2T<REAL>::type slot[2][NPTS];            // (f+, f-) of the staged plane
-    REAL exch_hn_y[TY][TX], exch_hp_y[TY][TX];
-    REAL edge_hn_x[TY], edge_hp_x[TY], edge_hn_y[TX], edge_hp_y[TX];
-};
-
-template <typename REAL, int W, int MODE, int TY, int MINB>
-__global__ void __launch_bounds__(32 * (TY + 1), MINB)
-burgers3d_stage_tiled(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
-                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
-{
-    typedef typename V2T<REAL>::type V2;
-    typedef BurgersTileSmem<REAL, TY> S;
-    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS;
-    constexpr int NT = 32 * (TY + 1);
-    constexpr int NPRE = (NPTS + NT - 1) / NT;
-    __shared__ __align__(16) S sm;
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int tid = ty * 32 + tx;
-    const bool edge_warp = (ty == TY);
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + tx, j = j0 + ty;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const long long P = a.pitch, Z = a.plane;
-    const bool in_dom = !edge_warp && i < a.nx && j < a.ny;
-    const long long col = (long long)i + P * j;
-
-    bool xact, yact, zact;
-    if (MODE == BMODE_MGPU) {
-        xact = (j >= 3 && j <= a.ny - 4) && (i >= 2 && i <= a.nx - 4);
-        yact = (i >= 3 && i <= a.nx - 4) && (j >= 2 && j <= a.ny - 4);
-        zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
-    } else {
-        xact = yact = zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
-    }
-
-    // tile point -> global offset for the cooperative plane fetch (constant over planes)
-    long long pre_off[NPRE];
-    bool pre_ok[NPRE];
-#pragma unroll
-    for (int n = 0; n < NPRE; n++) {
-        const int idx = tid + n * NT;
-        const int r = idx / RP, c = idx - r * RP;
-        const int gi = i0 - H + c, gj = j0 - H + r;
-        pre_ok[n] = idx < NPTS && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
-        pre_off[n] = (long long)gi + P * gj;
-    }
-    REAL pre[NPRE];
-    auto fetch = [&](int p) {
-        const bool pl = (p >= 0 && p < a.nzs);
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) pre[n] = (pl && pre_ok[n]) ? u[pre_off[n] + Z * p] : REAL(0);
-    };
-    auto park = [&](int s) {
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) {
-            const int idx = tid + n * NT;
-            if (idx < NPTS) sm.slot[s][idx] = lf_split<REAL>(pre[n]);
-        }
-    };
-
-    const int p_first = kb - 3, p_last = ke + 2;
-    fetch(p_first);
-    park(p_first & 1);
-    __syncthreads();
-
-    V2 z0, z1, z2, z3, z4;                      // (f+,f-) of planes p-4..p for this column
-    z0.x = z0.y = z1.x = z1.y = z2.x = z2.y = z3.x = z3.y = z4.x = z4.y = REAL(0);
-    REAL L1 = 0, L2 = 0, L3 = 0;                // Lxy of planes p-1, p-2, p-3
-    REAL hn_z_prev = 0, Fz_prev = 0;
-
-    for (int p = p_first; p <= p_last; p++) {
-        const int s = p & 1;
-        if (p < p_last) fetch(p + 1);           // next plane's u -> registers, consumed at the bottom
-        const V2* __restrict__ sl = sm.slot[s];
-        const bool xy_plane = (p >= kb && p < ke && p >= a.own_lo && p < a.own_hi);   // CTA-uniform
-        REAL hn_x = 0, hp_x = 0, hn_y = 0, hp_y = 0, hpR = 0, hnL = 0;
-        V2 c;
-        c.x = c.y = REAL(0);
-        if (!edge_warp) {
-            const int o = (ty + H) * RP + tx + H;
-            c = sl[o];
-            if (xy_plane) {
-                const V2 xm2 = sl[o - 2], xm1 = sl[o - 1], xp1 = sl[o + 1], xp2 = sl[o + 2];
-                hn_x = weno_side<REAL, W>(xm2.x, xm1.x, c.x, xp1.x, xp2.x);
-                hp_x = weno_side<REAL, W>(xp2.y, xp1.y, c.y, xm1.y, xm2.y);
-                const V2 ym2 = sl[o - 2 * RP], ym1 = sl[o - RP], yp1 = sl[o + RP], yp2 = sl[o + 2 * RP];
-                hn_y = weno_side<REAL, W>(ym2.x, ym1.x, c.x, yp1.x, yp2.x);
-                hp_y = weno_side<REAL, W>(yp2.y, yp1.y, c.y, ym1.y, ym2.y);
-                sm.exch_hn_y[ty][tx] = hn_y;
-                sm.exch_hp_y[ty][tx] = hp_y;
-                hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-            }
-        } else if (xy_plane) {
-            // rim of the tile: hn at column -1 / row -1, hp at column TX / row TY
-#pragma unroll
-            for (int it = tx; it < 2 * (TX + TY); it += 32) {
-                int oc, st;               // centre offset in the slot, stencil stride
-                bool minus;
-                if (it < TY)               { oc = (it + H) * RP + (H - 1);            st = 1;  minus = true;  }
-                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);      st = 1;  minus = false; }
-                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);   st = RP; minus = true;  }
-                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
-                const V2 m2 = sl[oc - 2 * st], m1 = sl[oc - st], cc = sl[oc], p1 = sl[oc + st], p2 = sl[oc + 2 * st];
-                // one evaluation for either side: hp(a,b,c,d,e) == hn(e,d,c,b,a)
-                const REAL v = weno_side<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                  minus ? p1.x : m1.y, minus ? p2.x : m2.y);
-                if (it < TY) sm.edge_hn_x[it] = v;
-                else if (it < 2 * TY) sm.edge_hp_x[it - TY] = v;
-                else if (it < 2 * TY + TX) sm.edge_hn_y[it - 2 * TY] = v;
-                else sm.edge_hp_y[it - 2 * TY - TX] = v;
-            }
-        }
-        __syncthreads();                        // exchange arrays complete
-
-        if (!edge_warp) {
-            REAL Lxy = REAL(0);
-            if (xy_plane) {
-                if (tx == 31) hpR = sm.edge_hp_x[ty];
-                if (tx == 0) hnL = sm.edge_hn_x[ty];
-                if (xact) {
-                    const REAL fu = hn_x + hpR;
-                    const REAL fu_old = (MODE == BMODE_MGPU && i == 2) ? REAL(0) : hnL + hp_x;
-                    Lxy = -(fu - fu_old) * a.rdx;
-                }
-                if (yact) {
-                    const REAL hnD = (ty == 0) ? sm.edge_hn_y[tx] : sm.exch_hn_y[ty - 1][tx];
-                    const REAL hpU = (ty == TY - 1) ? sm.edge_hp_y[tx] : sm.exch_hp_y[ty + 1][tx];
-                    const REAL gu = hn_y + hpU;
-                    const REAL gu_old = (MODE == BMODE_MGPU && j == 2) ? REAL(0) : hnD + hp_y;
-                    Lxy -= (gu - gu_old) * a.rdy;
-                }
-            }
-            // z: queue now holds planes p-4..p; pair centred on m = p-2 closes face m-1/2
-            z0 = z1; z1 = z2; z2 = z3; z3 = z4; z4 = c;
-            const int q = p - 3;                // the cell finished in this iteration
-            REAL Fz = 0, hn_z = 0;
-            if (p >= kb + 1) {                  // CTA-uniform
-                hn_z = weno_side<REAL, W>(z0.x, z1.x, z2.x, z3.x, z4.x);
-                const REAL hp_z = weno_side<REAL, W>(z4.y, z3.y, z2.y, z1.y, z0.y);
-                Fz = hn_z_prev + hp_z;
-            }
-            if (q >= kb && in_dom) {
-                const long long o = col + Z * q;
-                const REAL uq = u[o];
-                const bool owned = (q >= a.own_lo && q < a.own_hi);
-                const bool rk = (MODE == BMODE_MGPU) ? true : (owned && zact);
-                REAL res = uq;
-                if (rk) {
-                    REAL Lu = L3;
-                    if (owned) {
-                        if (MODE == BMODE_MGPU && j == 2 && yact) {
-                            const long long ra = (long long)i + P * q;
-                            if (a.stage > 1) Lu += rowacc[ra];
-                            rowacc[ra] = Lu;
-                        }
-                        if (zact) Lu -= (Fz - Fz_prev) * a.rdz;
-                    }
-                    const REAL qo = (a.stage == 1) ? uq : uo[o];
-                    const REAL t = uq + a.dt * Lu;
-                    res = (a.stage == 1) ? qo + a.dt * Lu
-                        : (a.stage == 2) ? REAL(0.75) * qo + REAL(0.25) * t
-                                         : (qo + REAL(2) * t) * REAL(1.0 / 3.0);
-                }
-                out[o] = res;
-            }
-            Fz_prev = Fz; hn_z_prev = hn_z;
-            L3 = L2; L2 = L1; L1 = Lxy;
-        }
-        if (p < p_last) park((p + 1) & 1);
-        __syncthreads();                        // next slot visible; exchange arrays free again
-    }
-}
-
-
-// =============================================================================================
-// v3 ("ring"): same algorithm as v2, restructured for the issue slot and the barrier.
-//  - the z stencil is read from a 7-slot shared-memory ring of (f+,f-) planes instead of per-thread
-//    register queues: the only loop-carried values are the lower z-face flux and two x partial sums;
-//  - the (hn,hp) halves of plane m+1 are produced in iteration m and consumed in iteration m+1, so
-//    one __syncthreads per plane is enough;
-//  - WENO constants come from the kernel-parameter constant bank, cell activity is predication.
-// Iteration m finishes plane m: planes m-2..m+3 live in the ring, plane m+4 is being staged.
-// =============================================================================================
-template <typename REAL, int W>
-__device__ __forceinline__ REAL weno_side_c(REAL a, REAL b, REAL c, REAL d, REAL e, const REAL* __restrict__ wc)
-{
-    const REAL t0 = (a - 2 * b) + c, s0 = (a - 4 * b) + 3 * c;
-    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
-    const REAL t2 = (c - 2 * d) + e, s2 = (3 * c - 4 * d) + e;
-    const REAL q0 = wc[9] * a - wc[10] * b + wc[11] * c;
-    const REAL q1 = wc[13] * c - wc[12] * b + wc[9] * d;
-    const REAL q2 = wc[9] * c + wc[13] * d - wc[12] * e;
-    const REAL E0 = (wc[0] * t0) * t0 + ((wc[3] * s0) * s0 + wc[6]);
-    const REAL E1 = (wc[1] * t1) * t1 + ((wc[4] * s1) * s1 + wc[7]);
-    const REAL E2 = (wc[2] * t2) * t2 + ((wc[5] * s2) * s2 + wc[8]);
-    if (W == WENO_JS) {
-        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
-        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
-        return fast_div(q0 * n0 + (q1 * n1 + q2 * n2), (n0 + n1) + n2);
-    } else {
-        const REAL tau = fabs(E0 - E2);
-        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
-        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
-        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
-        return fast_div(q0 * A0 + (q1 * A1 + q2 * A2), (A0 + A1) + A2);
-    }
-}
-
-template <typename REAL, int TY>
-struct BurgersRingSmem {
-    static constexpr int TX = 32, H = 3, NSLOT = 7;
-    static constexpr int RP = TX + 2 * H, ROWS = TY + 2 * H, NPTS = RP * ROWS;
-    typename V2T<REAL>::type slot[NSLOT][NPTS];
-    REAL hn_y[2][TY + 2][TX], hp_y[2][TY + 2][TX];     // row r+1 <-> tile row r; rows 0 / TY+1: rim
-    REAL edge_hn_x[2][TY], edge_hp_x[2][TY];
-};
-
-template <typename REAL, int W, int MODE, int TY, int MINB>
-__global__ void __launch_bounds__(32 * (TY + 1), MINB)
-burgers3d_stage_ring(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
-                     REAL* __restrict__ out, REAL* __restrict__ rowacc)
-{
-    typedef typename V2T<REAL>::type V2;
-    typedef BurgersRingSmem<REAL, TY> S;
-    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS, NSLOT = S::NSLOT;
-    constexpr int NT = 32 * (TY + 1);
-    constexpr int NPRE = (NPTS + NT - 1) / NT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    S& sm = *reinterpret_cast<S*>(smem_raw);
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int tid = ty * 32 + tx;
-    const bool edge_warp = (ty == TY);
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + tx, j = j0 + ty;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const long long P = a.pitch, Z = a.plane;
-    const bool in_dom = !edge_warp && i < a.nx && j < a.ny;
-    const long long col = (long long)i + P * j;
-    const REAL* __restrict__ wc = a.wc;
-
-    bool xact, yact, zact;
-    if (MODE == BMODE_MGPU) {
-        xact = (j >= 3 && j <= a.ny - 4) && (i >= 2 && i <= a.nx - 4);
-        yact = (i >= 3 && i <= a.nx - 4) && (j >= 2 && j <= a.ny - 4);
-        zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
-    } else {
-        xact = yact = zact = (i >= 3 && i <= a.nx - 4) && (j >= 3 && j <= a.ny - 4);
-    }
-    const bool x_seed0 = (MODE == BMODE_MGPU) && i == 2;     // f_old = 0 at the first marched cell
-    const bool y_seed0 = (MODE == BMODE_MGPU) && j == 2;
-    const bool rowacc_cell = (MODE == BMODE_MGPU) && j == 2 && yact && in_dom;
-
-    long long pre_off[NPRE];
-    bool pre_ok[NPRE];
-#pragma unroll
-    for (int n = 0; n < NPRE; n++) {
-        const int idx = tid + n * NT;
-        const int r = idx / RP, c = idx - r * RP;
-        const int gi = i0 - H + c, gj = j0 - H + r;
-        pre_ok[n] = idx < NPTS && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
-        pre_off[n] = (long long)gi + P * gj;
-    }
-    REAL pre[NPRE];
-    auto fetch = [&](int p) {
-        const bool pl = (p >= 0 && p < a.nzs);
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) pre[n] = (pl && pre_ok[n]) ? u[pre_off[n] + Z * p] : REAL(0);
-    };
-    auto park = [&](int sidx) {
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) {
-            const int idx = tid + n * NT;
-            if (idx < NPTS) {
-                const REAL v = pre[n], sq = v * v;
-                V2 r;
-                r.x = (v >= 0 ? wc[14] : -wc[15]) * sq;
-                r.y = (v >= 0 ? -wc[15] : wc[14]) * sq;
-                sm.slot[sidx][idx] = r;
-            }
-        }
-    };
-    const int own = (ty + H) * RP + tx + H;       // this thread's cell inside a slot (compute warps)
-
-    // ---- prologue: planes kb-3..kb+2 -> slots 0..5, lower z face of plane kb
-    for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
-    __syncthreads();
-    REAL Fz_prev = REAL(0);
-    if (!edge_warp) {
-        const V2 v0 = sm.slot[0][own], v1 = sm.slot[1][own], v2 = sm.slot[2][own], v3 = sm.slot[3][own],
-                 v4 = sm.slot[4][own], v5 = sm.slot[5][own];
-        Fz_prev = weno_side_c<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_c<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-    }
-
-    REAL X1 = REAL(0), X2 = REAL(0);              // x face sums of the plane produced last iteration
-    REAL u_nxt = REAL(0), uo_nxt = REAL(0);       // own-cell u / uo of plane m+1, fetched a plane ahead
-    if (in_dom) { u_nxt = u[col + Z * kb]; uo_nxt = (a.stage == 1) ? u_nxt : uo[col + Z * kb]; }
-    int s0 = 0;                                   // slot of plane m-2
-
-    for (int m = kb - 1; m < ke; m++) {
-        auto sl = [&](int d) -> const V2* { int t = s0 + d; t = t >= NSLOT ? t - NSLOT : t; return sm.slot[t]; };
-        const bool do_final = (m >= kb);
-        const bool own_m = (m >= a.own_lo && m < a.own_hi);
-        const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
-        const bool do_fetch = (m + 4 <= ke + 2);
-        const int eb = m & 1, nb = eb ^ 1;
-        if (do_fetch) fetch(m + 4);
-        const REAL u_m = u_nxt, uo_m = uo_nxt;
-        if (in_dom && m + 1 < ke) {
-            u_nxt = u[col + Z * (m + 1)];
-            uo_nxt = (a.stage == 1) ? u_nxt : uo[col + Z * (m + 1)];
-        }
-
-        if (!edge_warp) {
-            if (do_final) {
-                // (1) x/y divergence of plane m from the halves produced in the previous iteration
-                REAL Lu = REAL(0);
-                if (own_m) {
-                    const REAL fu = (tx == 31) ? X1 + sm.edge_hp_x[eb][ty] : X1;
-                    REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][ty] + X2 : X2;
-                    fu_old = x_seed0 ? REAL(0) : fu_old;
-                    const REAL Lx = -(fu - fu_old) * a.rdx;
-                    const REAL gu = sm.hn_y[eb][ty + 1][tx] + sm.hp_y[eb][ty + 2][tx];
-                    REAL gu_old = sm.hn_y[eb][ty][tx] + sm.hp_y[eb][ty + 1][tx];
-                    gu_old = y_seed0 ? REAL(0) : gu_old;
-                    const REAL Ly = (gu - gu_old) * a.rdy;
-                    Lu = xact ? Lx : REAL(0);
-                    Lu = yact ? Lu - Ly : Lu;
-                }
-                // (2) upper z face of plane m: hn(m) from planes m-2..m+2, hp(m+1) from m-1..m+3
-                REAL Fz = REAL(0);
-                if (m >= a.own_lo - 1 && m < a.own_hi) {
-                    const V2 v0 = sl(0)[own], v1 = sl(1)[own], v2 = sl(2)[own], v3 = sl(3)[own], v4 = sl(4)[own], v5 = sl(5)[own];
-                    Fz = weno_side_c<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_c<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-                }
-                // (3) finish cell (i,j,m)
-                if (in_dom) {
-                    const long long o = col + Z * m;
-                    const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && zact);
-                    if (own_m) {
-                        if (rowacc_cell) {
-                            const long long ra = (long long)i + P * m;
-                            if (a.stage > 1) Lu += rowacc[ra];
-                            rowacc[ra] = Lu;
-                        }
-                        Lu = zact ? Lu - (Fz - Fz_prev) * a.rdz : Lu;
-                    }
-                    const REAL t = u_m + a.dt * Lu;
-                    const REAL r1 = uo_m + a.dt * Lu;
-                    const REAL r2 = wc[14] * uo_m + wc[15] * t;
-                    const REAL r3 = (uo_m + REAL(2) * t) * wc[19];
-                    const REAL res = (a.stage == 1) ? r1 : (a.stage == 2) ? r2 : r3;
-                    out[o] = rk ? res : u_m;
-                }
-                Fz_prev = Fz;
-            }
-            // (4) halves of plane m+1 for the next iteration
-            if (do_pairs) {
-                const V2* __restrict__ s3 = sl(3);
-                const V2 c = s3[own];
-                const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
-                const REAL hn_x = weno_side_c<REAL, W>(xm2.x, xm1.x, c.x, xp1.x, xp2.x, wc);
-                const REAL hp_x = weno_side_c<REAL, W>(xp2.y, xp1.y, c.y, xm1.y, xm2.y, wc);
-                const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
-                sm.hn_y[nb][ty + 1][tx] = weno_side_c<REAL, W>(ym2.x, ym1.x, c.x, yp1.x, yp2.x, wc);
-                sm.hp_y[nb][ty + 1][tx] = weno_side_c<REAL, W>(yp2.y, yp1.y, c.y, ym1.y, ym2.y, wc);
-                const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-                X1 = (tx == 31) ? hn_x : hn_x + hpR;       // f_{i+1/2} = hn(i) + hp(i+1)
-                X2 = (tx == 0) ? hp_x : hnL + hp_x;        // f_{i-1/2} = hn(i-1) + hp(i)
-            }
-        } else if (do_pairs) {
-            const V2* __restrict__ s3 = sl(3);
-#pragma unroll 1
-            for (int it = tx; it < 2 * (TX + TY); it += 32) {
-                int oc, st;
-                bool minus;
-                if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
-                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
-                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
-                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
-                const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
-                const REAL v = weno_side_c<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
-                if (it < TY) sm.edge_hn_x[nb][it] = v;
-                else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
-                else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
-                else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
-            }
-        }
-        // (5) stage plane m+4 into the slot plane m-3 used to occupy
-        if (do_fetch) { int t = s0 + 6; t = t >= NSLOT ? t - NSLOT : t; park(t); }
-        __syncthreads();
-        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
-    }
-}
-
-
-// =============================================================================================
-// v4 ("ring, CPT cells per thread"): the ring kernel with each thread owning CPT cells of a column
-// pair (rows ty, ty+TY/CPT, ...) so that independent reconstructions interleave (ILP instead of
-// more warps) and loop control / constants / addressing are amortised over CPT cells, and with the
-// WENO value written as the central candidate plus a correction by third differences:
-//     h = q1 + [2 (t0-t1) n0 + (t1-t2) n2] / (6 (n0+n1+n2)),  n_k = prod_{m!=k} P_m,
-// (q0-q1 = (t0-t1)/3, q2-q1 = (t1-t2)/6), which needs one reciprocal and ~44 FP64 instructions per
-// side instead of ~50, and is better conditioned in smooth regions (the correction is small).
-// =============================================================================================
 __device__ __forceinline__ double fast_rcp(double den)
 {
     double y;
@@ -673,256 +204,6 @@ __device__ __forceinline__ double fast_rcp(double den)
 }
 __device__ __forceinline__ float fast_rcp(float den) { return __frcp_rn(den); }
 
-template <typename REAL, int W>
-__device__ __forceinline__ REAL weno_side_d(REAL a, REAL b, REAL c, REAL d, REAL e, const REAL* __restrict__ wc)
-{
-    const REAL t0 = (a - 2 * b) + c, s0 = (a - 4 * b) + 3 * c;
-    const REAL t1 = (b - 2 * c) + d, s1 = b - d;
-    const REAL t2 = (c - 2 * d) + e, s2 = (3 * c - 4 * d) + e;
-    const REAL q1 = wc[13] * c - wc[12] * b + wc[9] * d;              // (-b + 5c + 2d)/6
-    const REAL E0 = (wc[0] * t0) * t0 + ((wc[3] * s0) * s0 + wc[6]);
-    const REAL E1 = (wc[1] * t1) * t1 + ((wc[4] * s1) * s1 + wc[7]);
-    const REAL E2 = (wc[2] * t2) * t2 + ((wc[5] * s2) * s2 + wc[8]);
-    const REAL d01 = t0 - t1, d12 = t1 - t2;
-    if (W == WENO_JS) {
-        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;
-        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
-        const REAL A = d01 * n0;
-        const REAL num = d12 * n2 + (A + A);
-        const REAL den6 = REAL(6) * ((n0 + n1) + n2);
-        return num * fast_rcp(den6) + q1;
-    } else {
-        const REAL tau = fabs(E0 - E2);
-        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
-        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
-        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
-        const REAL A = d01 * A0;
-        const REAL num = d12 * A2 + (A + A);
-        const REAL den6 = REAL(6) * ((A0 + A1) + A2);
-        return num * fast_rcp(den6) + q1;
-    }
-}
-
-template <typename REAL, int TY>
-struct BurgersRing2Smem {
-    static constexpr int TX = 32, H = 3, NSLOT = 7;
-    static constexpr int RP = TX + 2 * H, ROWS = TY + 2 * H, NPTS = RP * ROWS;
-    typename V2T<REAL>::type slot[NSLOT][NPTS];
-    REAL hn_y[2][TY + 2][TX], hp_y[2][TY + 2][TX];
-    REAL edge_hn_x[2][TY], edge_hp_x[2][TY];
-};
-
-template <typename REAL, int W, int MODE, int TY, int CPT, int MINB>
-__global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
-burgers3d_stage_ring2(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
-                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
-{
-    typedef typename V2T<REAL>::type V2;
-    typedef BurgersRing2Smem<REAL, TY> S;
-    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS, NSLOT = S::NSLOT;
-    constexpr int NW = TY / CPT;                 // compute warps; warp NW is the edge warp
-    constexpr int NT = 32 * (NW + 1);
-    constexpr int NPRE = (NPTS + NT - 1) / NT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    S& sm = *reinterpret_cast<S*>(smem_raw);
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int tid = ty * 32 + tx;
-    const bool edge_warp = (ty == NW);
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + tx;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const long long P = a.pitch, Z = a.plane;
-    const REAL* __restrict__ wc = a.wc;
-    const bool i_in3 = (i >= 3 && i <= a.nx - 4);
-    const bool x_seed0 = (MODE == BMODE_MGPU) && i == 2;
-
-    // per-cell (row) activity of this thread's CPT cells: rows r_c = ty + c*NW
-    bool xact[CPT], yact[CPT], zact[CPT], in_dom[CPT];
-    long long col[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        const int j = j0 + ty + c * NW;
-        const bool j_in3 = (j >= 3 && j <= a.ny - 4);
-        if (MODE == BMODE_MGPU) {
-            xact[c] = j_in3 && (i >= 2 && i <= a.nx - 4);
-            yact[c] = i_in3 && (j >= 2 && j <= a.ny - 4);
-        } else {
-            xact[c] = yact[c] = i_in3 && j_in3;
-        }
-        zact[c] = i_in3 && j_in3;
-        in_dom[c] = !edge_warp && i < a.nx && j < a.ny;
-        col[c] = (long long)i + P * j;
-    }
-
-    long long pre_off[NPRE];
-    bool pre_ok[NPRE];
-#pragma unroll
-    for (int n = 0; n < NPRE; n++) {
-        const int idx = tid + n * NT;
-        const int r = idx / RP, cc = idx - r * RP;
-        const int gi = i0 - H + cc, gj = j0 - H + r;
-        pre_ok[n] = idx < NPTS && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
-        pre_off[n] = (long long)gi + P * gj;
-    }
-    REAL pre[NPRE];
-    auto fetch = [&](int p) {
-        const bool pl = (p >= 0 && p < a.nzs);
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) pre[n] = (pl && pre_ok[n]) ? u[pre_off[n] + Z * p] : REAL(0);
-    };
-    auto park = [&](int sidx) {
-#pragma unroll
-        for (int n = 0; n < NPRE; n++) {
-            const int idx = tid + n * NT;
-            if (idx < NPTS) {
-                const REAL v = pre[n], sq = v * v;
-                V2 r;
-                r.x = (v >= 0 ? wc[14] : -wc[15]) * sq;
-                r.y = (v >= 0 ? -wc[15] : wc[14]) * sq;
-                sm.slot[sidx][idx] = r;
-            }
-        }
-    };
-    const int own0 = (ty + H) * RP + tx + H;      // cell c lives at own0 + c*NW*RP
-
-    for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
-    __syncthreads();
-    REAL Fz_prev[CPT], X1[CPT], X2[CPT], u_nxt[CPT], uo_nxt[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        Fz_prev[c] = X1[c] = X2[c] = u_nxt[c] = uo_nxt[c] = REAL(0);
-        if (!edge_warp) {
-            const int own = own0 + c * NW * RP;
-            const V2 v0 = sm.slot[0][own], v1 = sm.slot[1][own], v2 = sm.slot[2][own], v3 = sm.slot[3][own],
-                     v4 = sm.slot[4][own], v5 = sm.slot[5][own];
-            Fz_prev[c] = weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-        }
-        if (in_dom[c]) { u_nxt[c] = u[col[c] + Z * kb]; uo_nxt[c] = (a.stage == 1) ? u_nxt[c] : uo[col[c] + Z * kb]; }
-    }
-    int s0 = 0;
-
-    for (int m = kb - 1; m < ke; m++) {
-        auto sl = [&](int d) -> const V2* { int t = s0 + d; t = t >= NSLOT ? t - NSLOT : t; return sm.slot[t]; };
-        const bool do_final = (m >= kb);
-        const bool own_m = (m >= a.own_lo && m < a.own_hi);
-        const bool do_z = (m >= a.own_lo - 1 && m < a.own_hi);
-        const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
-        const bool do_fetch = (m + 4 <= ke + 2);
-        const int eb = m & 1, nb = eb ^ 1;
-        if (do_fetch) fetch(m + 4);
-        REAL u_m[CPT], uo_m[CPT];
-#pragma unroll
-        for (int c = 0; c < CPT; c++) {
-            u_m[c] = u_nxt[c]; uo_m[c] = uo_nxt[c];
-            if (in_dom[c] && m + 1 < ke) {
-                u_nxt[c] = u[col[c] + Z * (m + 1)];
-                uo_nxt[c] = (a.stage == 1) ? u_nxt[c] : uo[col[c] + Z * (m + 1)];
-            }
-        }
-
-        if (!edge_warp) {
-            if (do_final) {
-                const V2 *p0 = sl(0), *p1 = sl(1), *p2 = sl(2), *p3 = sl(3), *p4 = sl(4), *p5 = sl(5);
-#pragma unroll
-                for (int c = 0; c < CPT; c++) {
-                    const int r = ty + c * NW;
-                    const int own = own0 + c * NW * RP;
-                    REAL Lu = REAL(0);
-                    if (own_m) {
-                        const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
-                        REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
-                        fu_old = x_seed0 ? REAL(0) : fu_old;
-                        const REAL Lx = -(fu - fu_old) * a.rdx;
-                        const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
-                        REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                        gu_old = ((MODE == BMODE_MGPU) && (j0 + r == 2)) ? REAL(0) : gu_old;
-                        const REAL Ly = (gu - gu_old) * a.rdy;
-                        Lu = xact[c] ? Lx : REAL(0);
-                        Lu = yact[c] ? Lu - Ly : Lu;
-                    }
-                    REAL Fz = REAL(0);
-                    if (do_z) {
-                        const V2 v0 = p0[own], v1 = p1[own], v2 = p2[own], v3 = p3[own], v4 = p4[own], v5 = p5[own];
-                        Fz = weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-                    }
-                    if (in_dom[c]) {
-                        const long long o = col[c] + Z * m;
-                        const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && zact[c]);
-                        if (own_m) {
-                            if ((MODE == BMODE_MGPU) && (j0 + r == 2) && yact[c]) {
-                                const long long ra = (long long)i + P * m;
-                                if (a.stage > 1) Lu += rowacc[ra];
-                                rowacc[ra] = Lu;
-                            }
-                            Lu = zact[c] ? Lu - (Fz - Fz_prev[c]) * a.rdz : Lu;
-                        }
-                        const REAL t = u_m[c] + a.dt * Lu;
-                        const REAL r1 = uo_m[c] + a.dt * Lu;
-                        const REAL r2 = wc[14] * uo_m[c] + wc[15] * t;
-                        const REAL r3 = (uo_m[c] + REAL(2) * t) * wc[19];
-                        const REAL res = (a.stage == 1) ? r1 : (a.stage == 2) ? r2 : r3;
-                        out[o] = rk ? res : u_m[c];
-                    }
-                    Fz_prev[c] = Fz;
-                }
-            }
-            if (do_pairs) {
-                const V2* __restrict__ s3 = sl(3);
-#pragma unroll
-                for (int c = 0; c < CPT; c++) {
-                    const int r = ty + c * NW;
-                    const int own = own0 + c * NW * RP;
-                    const V2 cc = s3[own];
-                    const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
-                    const REAL hn_x = weno_side_d<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
-                    const REAL hp_x = weno_side_d<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
-                    const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
-                    sm.hn_y[nb][r + 1][tx] = weno_side_d<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
-                    sm.hp_y[nb][r + 1][tx] = weno_side_d<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
-                    const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                    const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-                    X1[c] = (tx == 31) ? hn_x : hn_x + hpR;
-                    X2[c] = (tx == 0) ? hp_x : hnL + hp_x;
-                }
-            }
-        } else if (do_pairs) {
-            const V2* __restrict__ s3 = sl(3);
-#pragma unroll 1
-            for (int it = tx; it < 2 * (TX + TY); it += 32) {
-                int oc, st;
-                bool minus;
-                if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
-                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
-                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
-                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
-                const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
-                const REAL v = weno_side_d<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
-                if (it < TY) sm.edge_hn_x[nb][it] = v;
-                else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
-                else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
-                else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
-            }
-        }
-        if (do_fetch) { int t = s0 + 6; t = t >= NSLOT ? t - NSLOT : t; park(t); }
-        __syncthreads();
-        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
-    }
-}
-
-
-// =============================================================================================
-// v5 ("ring, split barrier"): v4 with
-//  - a split-phase mbarrier instead of __syncthreads: every thread ARRIVES at the end of plane m and
-//    only WAITS after it has computed the z faces of plane m+1, which depend on nothing other threads
-//    wrote (each compute thread stages its own cells of a plane itself; only halo points are staged
-//    by whoever is free), so barrier skew hides behind a quarter of the iteration's arithmetic;
-//  - pointers bumped by one plane per iteration instead of re-derived addresses;
-//  - no move that waits on the load it was just issued behind.
-// =============================================================================================
 __device__ __forceinline__ void mbar_init(unsigned addr, unsigned count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
@@ -931,271 +212,6 @@ __device__ __forceinline__ void mbar_arrive(unsigned addr)
 {
     asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(addr) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(unsigned addr, unsigned parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred P1;\n"
-        "MBAR_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-        "@P1 bra MBAR_DONE;\n"
-        "bra MBAR_WAIT;\n"
-        "MBAR_DONE:\n"
-        "}\n" ::"r"(addr), "r"(parity) : "memory");
-}
-
-template <typename REAL, int TY>
-struct BurgersRing3Smem {
-    static constexpr int TX = 32, H = 3, NSLOT = 7;
-    static constexpr int RP = TX + 2 * H, ROWS = TY + 2 * H, NPTS = RP * ROWS;
-    static constexpr int NHALO = 2 * H * RP + 2 * H * TY;
-    typename V2T<REAL>::type slot[NSLOT][NPTS];
-    REAL hn_y[2][TY + 2][TX], hp_y[2][TY + 2][TX];
-    REAL edge_hn_x[2][TY], edge_hp_x[2][TY];
-    unsigned long long bar;
-};
-
-template <typename REAL, int W, int MODE, int TY, int CPT, int MINB>
-__global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
-burgers3d_stage_ring3(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
-                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
-{
-    typedef typename V2T<REAL>::type V2;
-    typedef BurgersRing3Smem<REAL, TY> S;
-    constexpr int TX = S::TX, H = S::H, RP = S::RP, NPTS = S::NPTS, NSLOT = S::NSLOT, NHALO = S::NHALO;
-    constexpr int NW = TY / CPT;
-    constexpr int NT = 32 * (NW + 1);
-    constexpr int NPH = (NHALO + NT - 1) / NT;   // halo points staged per thread
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    S& sm = *reinterpret_cast<S*>(smem_raw);
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int tid = ty * 32 + tx;
-    const bool edge_warp = (ty == NW);
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + tx;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const long long P = a.pitch, Z = a.plane;
-    const REAL* __restrict__ wc = a.wc;
-    const bool i_in3 = (i >= 3 && i <= a.nx - 4);
-    const bool x_seed0 = (MODE == BMODE_MGPU) && i == 2;
-    const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.bar);
-
-    bool xact[CPT], yact[CPT], zact[CPT], in_dom[CPT];
-    long long col[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        const int j = j0 + ty + c * NW;
-        const bool j_in3 = (j >= 3 && j <= a.ny - 4);
-        if (MODE == BMODE_MGPU) {
-            xact[c] = j_in3 && (i >= 2 && i <= a.nx - 4);
-            yact[c] = i_in3 && (j >= 2 && j <= a.ny - 4);
-        } else {
-            xact[c] = yact[c] = i_in3 && j_in3;
-        }
-        zact[c] = i_in3 && j_in3;
-        in_dom[c] = !edge_warp && i < a.nx && j < a.ny;
-        col[c] = in_dom[c] ? (long long)i + P * j : 0;
-    }
-    // halo points of the tile this thread stages (slot index and global column offset)
-    int h_idx[NPH];
-    long long h_off[NPH];
-    bool h_ok[NPH];
-#pragma unroll
-    for (int n = 0; n < NPH; n++) {
-        const int hh = tid + n * NT;
-        int r, cc;
-        if (hh < H * RP) { r = hh / RP; cc = hh - r * RP; }
-        else if (hh < 2 * H * RP) { const int t = hh - H * RP; r = t / RP; cc = t - r * RP; r += H + TY; }
-        else { const int t = hh - 2 * H * RP; r = H + t / (2 * H); const int q = t - (t / (2 * H)) * (2 * H); cc = q < H ? q : TX + q; }
-        const int gi = i0 - H + cc, gj = j0 - H + r;
-        h_idx[n] = r * RP + cc;
-        h_ok[n] = hh < NHALO && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
-        h_off[n] = h_ok[n] ? (long long)gi + P * gj : 0;
-        if (hh >= NHALO) h_idx[n] = -1;
-    }
-    const int own0 = (ty + H) * RP + tx + H;
-
-    REAL st_own[CPT], st_halo[NPH];              // values being staged (one plane ahead of the park)
-    auto fetch = [&](int p) {
-        const bool pl = (p >= 0 && p < a.nzs);
-        const REAL* __restrict__ up = u + Z * p;
-#pragma unroll
-        for (int c = 0; c < CPT; c++) st_own[c] = (pl && in_dom[c]) ? up[col[c]] : REAL(0);
-#pragma unroll
-        for (int n = 0; n < NPH; n++) st_halo[n] = (pl && h_ok[n]) ? up[h_off[n]] : REAL(0);
-    };
-    auto split = [&](REAL v) -> V2 {
-        const REAL sq = v * v;
-        V2 r;
-        r.x = (v >= 0 ? wc[14] : -wc[15]) * sq;
-        r.y = (v >= 0 ? -wc[15] : wc[14]) * sq;
-        return r;
-    };
-    auto park = [&](int sidx) {
-        V2* __restrict__ sp = sm.slot[sidx];
-        if (!edge_warp) {
-#pragma unroll
-            for (int c = 0; c < CPT; c++) sp[own0 + c * NW * RP] = split(st_own[c]);
-        }
-#pragma unroll
-        for (int n = 0; n < NPH; n++) if (h_idx[n] >= 0) sp[h_idx[n]] = split(st_halo[n]);
-    };
-
-    if (tid == 0) mbar_init(bar, NT);
-    for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
-    __syncthreads();
-    REAL Fz_prev[CPT], X1[CPT], X2[CPT], u_nxt[CPT], uo_nxt[CPT];
-    const REAL *pu[CPT], *puo[CPT];
-    REAL* pout[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        Fz_prev[c] = X1[c] = X2[c] = u_nxt[c] = uo_nxt[c] = REAL(0);
-        if (!edge_warp) {
-            const int own = own0 + c * NW * RP;
-            const V2 v0 = sm.slot[0][own], v1 = sm.slot[1][own], v2 = sm.slot[2][own], v3 = sm.slot[3][own],
-                     v4 = sm.slot[4][own], v5 = sm.slot[5][own];
-            Fz_prev[c] = weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-        }
-        // bumped by one plane at the top of every iteration: inside iteration m they point at plane m+1 / m
-        pu[c] = u + col[c] + Z * (kb - 1);
-        puo[c] = uo + col[c] + Z * (kb - 1);
-        pout[c] = out + col[c] + Z * (kb - 2);
-    }
-    mbar_arrive(bar);
-    unsigned parity = 0;
-    int s0 = 0;
-
-    for (int m = kb - 1; m < ke; m++) {
-        auto sl = [&](int d) -> const V2* { int t = s0 + d; t = t >= NSLOT ? t - NSLOT : t; return sm.slot[t]; };
-        const bool do_final = (m >= kb);
-        const bool own_m = (m >= a.own_lo && m < a.own_hi);
-        const bool do_z = do_final && (m >= a.own_lo - 1 && m < a.own_hi);
-        const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
-        const bool do_fetch = (m + 4 <= ke + 2);
-        const int eb = m & 1, nb = eb ^ 1;
-        if (do_fetch) fetch(m + 4);
-        REAL u_m[CPT], uo_m[CPT];
-#pragma unroll
-        for (int c = 0; c < CPT; c++) {
-            u_m[c] = u_nxt[c]; uo_m[c] = uo_nxt[c];
-            pu[c] += Z; puo[c] += Z; pout[c] += Z;
-            if (in_dom[c] && m + 1 < ke) {
-                u_nxt[c] = *pu[c];
-                if (a.stage > 1) uo_nxt[c] = *puo[c];
-            }
-        }
-        // (A) upper z face of plane m -- own column only, nothing another thread wrote since the last wait
-        REAL Fz[CPT];
-#pragma unroll
-        for (int c = 0; c < CPT; c++) Fz[c] = REAL(0);
-        if (!edge_warp && do_z) {
-            const V2 *p0 = sl(0), *p1 = sl(1), *p2 = sl(2), *p3 = sl(3), *p4 = sl(4), *p5 = sl(5);
-#pragma unroll
-            for (int c = 0; c < CPT; c++) {
-                const int own = own0 + c * NW * RP;
-                const V2 v0 = p0[own], v1 = p1[own], v2 = p2[own], v3 = p3[own], v4 = p4[own], v5 = p5[own];
-                Fz[c] = weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-            }
-        }
-        // (B) everybody has finished plane m-1: halves of plane m and halo points are visible
-        mbar_wait(bar, parity);
-        parity ^= 1u;
-
-        if (!edge_warp) {
-            if (do_final) {
-#pragma unroll
-                for (int c = 0; c < CPT; c++) {
-                    const int r = ty + c * NW;
-                    REAL Lu = REAL(0);
-                    if (own_m) {
-                        const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
-                        REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
-                        fu_old = x_seed0 ? REAL(0) : fu_old;
-                        const REAL Lx = -(fu - fu_old) * a.rdx;
-                        const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
-                        REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                        gu_old = ((MODE == BMODE_MGPU) && (j0 + r == 2)) ? REAL(0) : gu_old;
-                        const REAL Ly = (gu - gu_old) * a.rdy;
-                        Lu = xact[c] ? Lx : REAL(0);
-                        Lu = yact[c] ? Lu - Ly : Lu;
-                    }
-                    if (in_dom[c]) {
-                        const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && zact[c]);
-                        if (own_m) {
-                            if ((MODE == BMODE_MGPU) && (j0 + r == 2) && yact[c]) {
-                                const long long ra = (long long)i + P * m;
-                                if (a.stage > 1) Lu += rowacc[ra];
-                                rowacc[ra] = Lu;
-                            }
-                            Lu = zact[c] ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz : Lu;
-                        }
-                        const REAL uo_c = (a.stage == 1) ? u_m[c] : uo_m[c];
-                        const REAL t = u_m[c] + a.dt * Lu;
-                        const REAL r1 = uo_c + a.dt * Lu;
-                        const REAL r2 = wc[14] * uo_c + wc[15] * t;
-                        const REAL r3 = (uo_c + REAL(2) * t) * wc[19];
-                        const REAL res = (a.stage == 1) ? r1 : (a.stage == 2) ? r2 : r3;
-                        *pout[c] = rk ? res : u_m[c];
-                    }
-                    Fz_prev[c] = Fz[c];
-                }
-            }
-            if (do_pairs) {
-                const V2* __restrict__ s3 = sl(3);
-#pragma unroll
-                for (int c = 0; c < CPT; c++) {
-                    const int r = ty + c * NW;
-                    const int own = own0 + c * NW * RP;
-                    const V2 cc = s3[own];
-                    const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
-                    const REAL hn_x = weno_side_d<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
-                    const REAL hp_x = weno_side_d<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
-                    const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
-                    sm.hn_y[nb][r + 1][tx] = weno_side_d<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
-                    sm.hp_y[nb][r + 1][tx] = weno_side_d<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
-                    const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                    const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-                    X1[c] = (tx == 31) ? hn_x : hn_x + hpR;
-                    X2[c] = (tx == 0) ? hp_x : hnL + hp_x;
-                }
-            }
-        } else if (do_pairs) {
-            const V2* __restrict__ s3 = sl(3);
-#pragma unroll 1
-            for (int it = tx; it < 2 * (TX + TY); it += 32) {
-                int oc, st;
-                bool minus;
-                if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
-                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
-                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
-                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
-                const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
-                const REAL v = weno_side_d<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
-                if (it < TY) sm.edge_hn_x[nb][it] = v;
-                else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
-                else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
-                else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
-            }
-        }
-        if (do_fetch) { int t = s0 + 6; t = t >= NSLOT ? t - NSLOT : t; park(t); }
-        mbar_arrive(bar);
-        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
-    }
-}
-
-
-// =============================================================================================
-// v6 ("ring, specialised"): v5 with the instruction overhead taken out of the inner loop:
-//  - the RK stage is a template parameter (one combine, not three plus selects);
-//  - tiles that lie entirely inside the update region (most of them) run a path with no per-cell
-//    activity predicates, seeds or scratch rows; rim tiles run the general path;
-//  - x halves are exchanged through shared memory like the y halves (rim columns written by the
-//    edge warp), which removes the lane-0/31 special cases and the loop-carried partial sums.
-// =============================================================================================
 __device__ __forceinline__ void mbar_wait_hint(unsigned addr, unsigned parity)
 {
     asm volatile(
@@ -1210,7 +226,7 @@ __device__ __forceinline__ void mbar_wait_hint(unsigned addr, unsigned parity)
 }
 
 template <typename REAL, int TY>
-struct BurgersRing4Smem {
+struct BurgersRingSmem {
     static constexpr int TX = 32, H = 3, NSLOT = 7;
     static constexpr int RP = TX + 2 * H, ROWS = TY + 2 * H, NPTS = RP * ROWS;
     static constexpr int NHALO = 2 * H * RP + 2 * H * TY;
@@ -1229,276 +245,6 @@ __device__ __forceinline__ REAL rk_stage(REAL u_m, REAL uo_m, REAL Lu, REAL dt, 
     return (uo_m + REAL(2) * t) * wc[19];
 }
 
-template <typename REAL, int W, int MODE, int TY, int CPT, int MINB, int STAGE, bool PEER>
-__global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
-burgers3d_stage_ring4(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
-                      REAL* __restrict__ out, REAL* __restrict__ rowacc)
-{
-    typedef typename V2T<REAL>::type V2;
-    typedef BurgersRing4Smem<REAL, TY> S;
-    constexpr int TX = S::TX, H = S::H, RP = S::RP, NSLOT = S::NSLOT, NHALO = S::NHALO;
-    constexpr int NW = TY / CPT;
-    constexpr int NT = 32 * (NW + 1);
-    constexpr int NPH = (NHALO + NT - 1) / NT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    S& sm = *reinterpret_cast<S*>(smem_raw);
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int tid = ty * 32 + tx;
-    const bool edge_warp = (ty == NW);
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + tx;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const long long P = a.pitch, Z = a.plane;
-    const REAL* __restrict__ wc = a.wc;
-    const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.bar);
-    // every cell of the tile is a regular interior cell (gets all three flux differences, no seeds)
-    const bool interior = (i0 >= 3) && (i0 + TX - 1 <= a.nx - 4) && (j0 >= 3) && (j0 + TY - 1 <= a.ny - 4);
-
-    long long col[CPT];
-    bool in_dom[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        const int j = j0 + ty + c * NW;
-        in_dom[c] = !edge_warp && i < a.nx && j < a.ny;
-        col[c] = in_dom[c] ? (long long)i + P * j : 0;
-    }
-    int h_idx[NPH];
-    long long h_off[NPH];
-    bool h_ok[NPH];
-#pragma unroll
-    for (int n = 0; n < NPH; n++) {
-        const int hh = tid + n * NT;
-        int r, cc;
-        if (hh < H * RP) { r = hh / RP; cc = hh - r * RP; }
-        else if (hh < 2 * H * RP) { const int t = hh - H * RP; r = t / RP; cc = t - r * RP; r += H + TY; }
-        else { const int t = hh - 2 * H * RP; r = H + t / (2 * H); const int q = t - (t / (2 * H)) * (2 * H); cc = q < H ? q : TX + q; }
-        const int gi = i0 - H + cc, gj = j0 - H + r;
-        h_idx[n] = (hh < NHALO) ? r * RP + cc : -1;
-        h_ok[n] = hh < NHALO && gi >= 0 && gi < a.nx && gj >= 0 && gj < a.ny;
-        h_off[n] = h_ok[n] ? (long long)gi + P * gj : 0;
-    }
-    const int own0 = (ty + H) * RP + tx + H;
-
-    REAL st_own[CPT], st_halo[NPH];
-    auto fetch = [&](int p) {
-        const bool pl = (p >= 0 && p < a.nzs);
-        const REAL* __restrict__ up = u + Z * p;
-#pragma unroll
-        for (int c = 0; c < CPT; c++) st_own[c] = (pl && in_dom[c]) ? up[col[c]] : REAL(0);
-#pragma unroll
-        for (int n = 0; n < NPH; n++) st_halo[n] = (pl && h_ok[n]) ? up[h_off[n]] : REAL(0);
-    };
-    auto split = [&](REAL v) -> V2 {
-        const REAL sq = v * v;
-        V2 r;
-        r.x = (v >= 0 ? wc[14] : -wc[15]) * sq;
-        r.y = (v >= 0 ? -wc[15] : wc[14]) * sq;
-        return r;
-    };
-    auto park = [&](int sidx) {
-        V2* __restrict__ sp = sm.slot[sidx];
-        if (!edge_warp) {
-#pragma unroll
-            for (int c = 0; c < CPT; c++) sp[own0 + c * NW * RP] = split(st_own[c]);
-        }
-#pragma unroll
-        for (int n = 0; n < NPH; n++) if (h_idx[n] >= 0) sp[h_idx[n]] = split(st_halo[n]);
-    };
-    auto zface = [&](const V2* p0, const V2* p1, const V2* p2, const V2* p3, const V2* p4, const V2* p5, int own) -> REAL {
-        const V2 v0 = p0[own], v1 = p1[own], v2 = p2[own], v3 = p3[own], v4 = p4[own], v5 = p5[own];
-        return weno_side_d<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc) + weno_side_d<REAL, W>(v5.y, v4.y, v3.y, v2.y, v1.y, wc);
-    };
-
-    // viscous 13-point term of the single-GPU target (Compute_Laplace_Async, SingleGPU/Burgers3d_WENO5/
-    // kernels.cu:471-473): needs u itself, which the ring does not hold -- read through L1/L2
-    auto visc13 = [&](const REAL* __restrict__ pc, REAL c0) -> REAL {
-        return a.kx * (-pc[-2] + 16 * pc[-1] - 30 * c0 + 16 * pc[1] - pc[2]) +
-               a.ky * (-pc[-2 * P] + 16 * pc[-P] - 30 * c0 + 16 * pc[P] - pc[2 * P]) +
-               a.kz * (-pc[-2 * Z] + 16 * pc[-Z] - 30 * c0 + 16 * pc[Z] - pc[2 * Z]);
-    };
-    if (tid == 0) mbar_init(bar, NT);
-    for (int d = 0; d < 6; d++) { fetch(kb - 3 + d); park(d); }
-    __syncthreads();
-    REAL Fz_prev[CPT], X1[CPT], X2[CPT], u_nxt[CPT], uo_nxt[CPT];
-    const REAL *pu[CPT], *puo[CPT];
-    REAL* pout[CPT];
-#pragma unroll
-    for (int c = 0; c < CPT; c++) {
-        u_nxt[c] = uo_nxt[c] = X1[c] = X2[c] = REAL(0);
-        Fz_prev[c] = edge_warp ? REAL(0)
-                               : zface(sm.slot[0], sm.slot[1], sm.slot[2], sm.slot[3], sm.slot[4], sm.slot[5], own0 + c * NW * RP);
-        pu[c] = u + col[c] + Z * (kb - 1);
-        puo[c] = uo + col[c] + Z * (kb - 1);
-        pout[c] = out + col[c] + Z * (kb - 2);
-    }
-    mbar_arrive(bar);
-    unsigned parity = 0;
-    int s0 = 0;
-
-    for (int m = kb - 1; m < ke; m++) {
-        auto sl = [&](int d) -> const V2* { int t = s0 + d; t = t >= NSLOT ? t - NSLOT : t; return sm.slot[t]; };
-        const bool do_final = (m >= kb);
-        const bool own_m = (m >= a.own_lo && m < a.own_hi);
-        const bool do_z = do_final && (m >= a.own_lo - 1 && m < a.own_hi);
-        const bool do_pairs = (m + 1 < ke) && (m + 1 >= a.own_lo && m + 1 < a.own_hi);
-        const bool do_fetch = (m + 4 <= ke + 2);
-        const int eb = m & 1, nb = eb ^ 1;
-        if (do_fetch) fetch(m + 4);
-        REAL u_m[CPT], uo_m[CPT];
-#pragma unroll
-        for (int c = 0; c < CPT; c++) {
-            u_m[c] = u_nxt[c]; uo_m[c] = uo_nxt[c];
-            pu[c] += Z; puo[c] += Z; pout[c] += Z;
-            if (in_dom[c] && m + 1 < ke) {
-                u_nxt[c] = *pu[c];
-                if (STAGE > 1) uo_nxt[c] = *puo[c];
-            }
-        }
-        REAL Fz[CPT];
-#pragma unroll
-        for (int c = 0; c < CPT; c++) Fz[c] = REAL(0);
-        if (!edge_warp && do_z) {
-            const V2 *p0 = sl(0), *p1 = sl(1), *p2 = sl(2), *p3 = sl(3), *p4 = sl(4), *p5 = sl(5);
-#pragma unroll
-            for (int c = 0; c < CPT; c++) Fz[c] = zface(p0, p1, p2, p3, p4, p5, own0 + c * NW * RP);
-        }
-        mbar_wait_hint(bar, parity);
-        parity ^= 1u;
-
-        if (!edge_warp) {
-            if (do_final) {
-                if (interior) {
-#pragma unroll
-                    for (int c = 0; c < CPT; c++) {
-                        const int r = ty + c * NW;
-                        REAL Lu = REAL(0);
-                        if (own_m) {
-                            const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
-                            const REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
-                            const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
-                            const REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                            Lu = -(fu - fu_old) * a.rdx;
-                            Lu -= (gu - gu_old) * a.rdy;
-                            Lu -= (Fz[c] - Fz_prev[c]) * a.rdz;
-                            if (MODE == BMODE_SGPU && a.visc) {
-                                const REAL term = visc13(pu[c] - Z, u_m[c]);
-                                Lu += term;
-                                if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
-                            }
-                        }
-                        const bool rk = (MODE == BMODE_MGPU) ? true : own_m;
-                        const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
-                        {
-                            const REAL val = rk ? res : u_m[c];
-                            *pout[c] = val;
-                            if (PEER) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
-                        }
-                        Fz_prev[c] = Fz[c];
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < CPT; c++) {
-                        const int r = ty + c * NW;
-                        const int j = j0 + r;
-                        const bool i_in3 = (i >= 3 && i <= a.nx - 4), j_in3 = (j >= 3 && j <= a.ny - 4);
-                        const bool xa = (MODE == BMODE_MGPU) ? (j_in3 && i >= 2 && i <= a.nx - 4) : (i_in3 && j_in3);
-                        const bool ya = (MODE == BMODE_MGPU) ? (i_in3 && j >= 2 && j <= a.ny - 4) : (i_in3 && j_in3);
-                        const bool za = i_in3 && j_in3;
-                        REAL Lu = REAL(0);
-                        if (own_m) {
-                            const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
-                            REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
-                            fu_old = ((MODE == BMODE_MGPU) && i == 2) ? REAL(0) : fu_old;
-                            const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
-                            REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                            gu_old = ((MODE == BMODE_MGPU) && j == 2) ? REAL(0) : gu_old;
-                            Lu = xa ? -(fu - fu_old) * a.rdx : REAL(0);
-                            Lu = ya ? Lu - (gu - gu_old) * a.rdy : Lu;
-                        }
-                        if (in_dom[c]) {
-                            const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && za);
-                            if (own_m) {
-                                if ((MODE == BMODE_MGPU) && j == 2 && ya) {
-                                    const long long ra = (long long)i + P * m;
-                                    if (STAGE > 1) Lu += rowacc[ra];
-                                    rowacc[ra] = Lu;
-                                }
-                                Lu = za ? Lu - (Fz[c] - Fz_prev[c]) * a.rdz : Lu;
-                                if (MODE == BMODE_SGPU && a.visc && za) {
-                                    const REAL term = visc13(pu[c] - Z, u_m[c]);
-                                    Lu += term;
-                                    if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
-                                }
-                            }
-                            const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
-                            {
-                            const REAL val = rk ? res : u_m[c];
-                            *pout[c] = val;
-                            if (PEER) a.out2[(pout[c] - out) + a.off2] = val;      // straight into the neighbour GPU's ghost plane
-                        }
-                        }
-                        Fz_prev[c] = Fz[c];
-                    }
-                }
-            }
-            if (do_pairs) {
-                const V2* __restrict__ s3 = sl(3);
-#pragma unroll
-                for (int c = 0; c < CPT; c++) {
-                    const int r = ty + c * NW;
-                    const int own = own0 + c * NW * RP;
-                    const V2 cc = s3[own];
-                    const V2 xm2 = s3[own - 2], xm1 = s3[own - 1], xp1 = s3[own + 1], xp2 = s3[own + 2];
-                    const REAL hn_x = weno_side_d<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
-                    const REAL hp_x = weno_side_d<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
-                    const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                    const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-                    X1[c] = (tx == 31) ? hn_x : hn_x + hpR;
-                    X2[c] = (tx == 0) ? hp_x : hnL + hp_x;
-                    const V2 ym2 = s3[own - 2 * RP], ym1 = s3[own - RP], yp1 = s3[own + RP], yp2 = s3[own + 2 * RP];
-                    sm.hn_y[nb][r + 1][tx] = weno_side_d<REAL, W>(ym2.x, ym1.x, cc.x, yp1.x, yp2.x, wc);
-                    sm.hp_y[nb][r + 1][tx] = weno_side_d<REAL, W>(yp2.y, yp1.y, cc.y, ym1.y, ym2.y, wc);
-                }
-            }
-        } else if (do_pairs) {
-            const V2* __restrict__ s3 = sl(3);
-#pragma unroll 1
-            for (int it = tx; it < 2 * (TX + TY); it += 32) {
-                int oc, st;
-                bool minus;
-                if (it < TY)               { oc = (it + H) * RP + (H - 1);                st = 1;  minus = true;  }
-                else if (it < 2 * TY)      { oc = (it - TY + H) * RP + (H + TX);          st = 1;  minus = false; }
-                else if (it < 2 * TY + TX) { oc = (H - 1) * RP + (it - 2 * TY + H);       st = RP; minus = true;  }
-                else                       { oc = (H + TY) * RP + (it - 2 * TY - TX + H); st = RP; minus = false; }
-                const V2 m2 = s3[oc - 2 * st], m1 = s3[oc - st], cc = s3[oc], p1 = s3[oc + st], p2 = s3[oc + 2 * st];
-                const REAL v = weno_side_d<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
-                if (it < TY) sm.edge_hn_x[nb][it] = v;
-                else if (it < 2 * TY) sm.edge_hp_x[nb][it - TY] = v;
-                else if (it < 2 * TY + TX) sm.hn_y[nb][0][it - 2 * TY] = v;
-                else sm.hp_y[nb][TY + 1][it - 2 * TY - TX] = v;
-            }
-        }
-        if (do_fetch) { int t = s0 + 6; t = t >= NSLOT ? t - NSLOT : t; park(t); }
-        mbar_arrive(bar);
-        s0 = (s0 + 1 == NSLOT) ? 0 : s0 + 1;
-    }
-}
-
-
-// =============================================================================================
-// v7 ("ring, steady state"): ring4 with the per-plane bookkeeping stripped from the steady state.
-// The kernel is issue-bound -- an FP64 instruction holds the issue port for two cycles, every other
-// instruction for one or more (tools/fp64_mix.cu: one IMAD per DFMA already costs a third of the FP64
-// peak) -- so what is left to gain is the count of non-FP64 instructions:
-//  - compute warps and the edge warp run separate loops (no role tests inside);
-//  - planes whose flags are all "on" in tiles that lie inside the update region run a body compiled
-//    without any of the window / ownership / domain / seed tests (FAST), everything else the general one;
-//  - one running plane offset instead of per-cell pointers; the split's sign test is an integer compare.
-// =============================================================================================
 // SIX TIMES the one-sided WENO5 value: 6h = (-b + 5c + 2d) + [2 (t0-t1) n0 + (t1-t2) n2] / (n0+n1+n2).
 // The candidate polynomial then has small-integer coefficients (immediates, no constant loads) and the
 // factor 6 of the denominator disappears; the caller multiplies the flux difference by 1/(6 dx).
@@ -1538,11 +284,11 @@ template <bool B> struct BoolTag { static constexpr bool value = B; };
 
 template <typename REAL, int W, int MODE, int TY, int CPT, int MINB, int STAGE, bool PEER>
 __global__ void __launch_bounds__(32 * (TY / CPT + 1), MINB)
-burgers3d_stage_ring5(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
+burgers3d_stage_ring(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
                       REAL* __restrict__ out, REAL* __restrict__ rowacc)
 {
     typedef typename V2T<REAL>::type V2;
-    typedef BurgersRing4Smem<REAL, TY> S;
+    typedef BurgersRingSmem<REAL, TY> S;
     constexpr int TX = S::TX, H = S::H, RP = S::RP, NSLOT = S::NSLOT, NHALO = S::NHALO;
     constexpr int NW = TY / CPT;
     constexpr int NT = 32 * (NW + 1);

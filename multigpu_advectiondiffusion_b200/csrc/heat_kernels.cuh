@@ -84,16 +84,7 @@ heat2d_stage_direct(HeatArgs<REAL> a, const REAL* __restrict__ u, const REAL* __
 
 }  // namespace adv
 
-// ---------------------------------------------------------------------------------------------
-// v2 ("tma"): TMA-staged tiles, 2.5-D streaming along z.
-//   - a CTA owns a TX x TY tile (two x-adjacent cells per thread) and marches a chunk of z planes;
-//   - each plane's tile + halo 2 is brought to shared memory by ONE cp.async.bulk.tensor.3d
-//     (zero fill outside the array), NST planes deep, completion on an mbarrier per stage;
-//   - the z stencil lives in a 5-deep register queue fed from the centre of the newest plane, the
-//     x/y stencil is read from the staged plane with 128-bit shared loads (both cells at once);
-//   - u_out (and uo for stages 2, 3) move as 128-bit coalesced accesses, uo one plane ahead.
-// Algorithmic traffic: 16 B (stage 1) / 24 B (stages 2, 3) per cell; halo re-reads are L2 hits.
-// ---------------------------------------------------------------------------------------------
+// TMA helpers (cp.async.bulk.tensor + mbarrier) used by the warp-specialised kernel below.
 #include <cuda.h>
 
 namespace adv {
@@ -139,129 +130,9 @@ __device__ __forceinline__ void mbar_wait_parity(unsigned bar, unsigned parity)
         "}\n" ::"r"(bar), "r"(parity) : "memory");
 }
 
-template <typename REAL, int TY, int NST>
-struct HeatTmaSmem {
-    static constexpr int TX = 64, H = 2;
-    // the x origin of a TMA box must fall on a 16-byte boundary of the row: halo of 2 doubles, but 4 floats
-    static constexpr int HX = (sizeof(REAL) == 8) ? 2 : 4;
-    static constexpr int BX = TX + 2 * HX, BY = TY + 2 * H;    // TMA box
-    struct alignas(128) Plane { REAL v[BY][BX]; };        // every TMA destination starts on 128 bytes
-    Plane stage[NST];
-    unsigned long long full[NST];
-};
-
-template <typename REAL, int TY, int NST, int STAGE>
-__global__ void __launch_bounds__(32 * TY)
-heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, HeatArgs<REAL> a, int chunk,
-                 const REAL* __restrict__ uo, REAL* __restrict__ out)
-{
-    typedef typename Vec2T<REAL>::type V2;
-    typedef HeatTmaSmem<REAL, TY, NST> S;
-    constexpr int TX = S::TX, H = S::H, HX = S::HX, BX = S::BX, BY = S::BY;
-    constexpr unsigned kBytes = BX * BY * sizeof(REAL);
-    extern __shared__ __align__(128) unsigned char heat_smem_raw[];
-    S& sm = *reinterpret_cast<S*>(heat_smem_raw);
-
-    const int tx = threadIdx.x, ty = threadIdx.y;
-    const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int i = i0 + 2 * tx, j = j0 + ty;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
-    if (kb >= ke) return;
-    const bool leader = (tx == 0 && ty == 0);
-    const bool in_dom = (i < a.nx) && (j < a.ny);          // nx is even on this path: both cells or none
-    const long long col = (long long)i + a.pitch * j;
-
-    if (leader) {
-        for (int s = 0; s < NST; s++) mbar_init_((unsigned)__cvta_generic_to_shared(&sm.full[s]), 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-
-    // planes are staged in order p = kb-2, kb-1, ...; plane p uses stage slot (p - (kb-2)) % NST
-    const int p_first = kb - 2, p_last = ke + 1;
-    auto issue = [&](int p) {                               // leader only
-        const int n = p - p_first;
-        const int s = n % NST;
-        const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.full[s]);
-        mbar_expect_tx(bar, kBytes);
-        tma_load_3d((unsigned)__cvta_generic_to_shared(&sm.stage[s].v[0][0]), &tmap, i0 - HX, j0 - H, p, bar);
-    };
-    if (leader) {
-        for (int p = p_first; p < p_first + NST && p <= p_last; p++) issue(p);
-    }
-
-    // per-cell masks (two cells: i and i+1)
-    const bool xl0 = i >= a.lap.lo[0] && i <= a.lap.hi[0], xl1 = i + 1 >= a.lap.lo[0] && i + 1 <= a.lap.hi[0];
-    const bool yl = j >= a.lap.lo[1] && j <= a.lap.hi[1];
-    const bool xr0 = i >= a.rk.lo[0] && i <= a.rk.hi[0], xr1 = i + 1 >= a.rk.lo[0] && i + 1 <= a.rk.hi[0];
-    const bool yr = j >= a.rk.lo[1] && j <= a.rk.hi[1];
-
-    V2 zm2, zm1, zc, zp1, zp2;                              // centres of planes k-2..k+2
-    zm2.x = zm2.y = zm1.x = zm1.y = zc.x = zc.y = zp1.x = zp1.y = zp2.x = zp2.y = REAL(0);
-    V2 uo_nxt;
-    uo_nxt.x = uo_nxt.y = REAL(0);
-    if (STAGE > 1 && in_dom) uo_nxt = *reinterpret_cast<const V2*>(uo + col + a.plane * kb);
-
-    // consume planes p = kb-2 .. ke+1; output plane k = p-2 once p >= kb+2
-    for (int p = p_first; p <= p_last; p++) {
-        const int n = p - p_first;
-        const int s = n % NST;
-        mbar_wait_parity((unsigned)__cvta_generic_to_shared(&sm.full[s]), (n / NST) & 1);
-        zm2 = zm1; zm1 = zc; zc = zp1; zp1 = zp2;
-        zp2 = *reinterpret_cast<const V2*>(&sm.stage[s].v[ty + H][2 * tx + HX]);
-        const int k = p - 2;
-        if (k >= kb) {
-            const int sk = (n - 2) % NST;                   // slot of plane k
-            const V2 uo_k = uo_nxt;
-            if (STAGE > 1 && in_dom && k + 1 < ke) uo_nxt = *reinterpret_cast<const V2*>(uo + col + a.plane * (k + 1));
-            V2 res = zc;
-            const bool zl = k >= a.lap.lo[2] && k <= a.lap.hi[2];
-            const bool zr = k >= a.rk.lo[2] && k <= a.rk.hi[2];
-            if (yr && zr) {
-                V2 Lu;
-                Lu.x = Lu.y = REAL(0);
-                if (yl && zl) {
-                    const REAL* row = &sm.stage[sk].v[ty + H][2 * tx + HX];
-                    const V2 xl = *reinterpret_cast<const V2*>(row - 2), xr = *reinterpret_cast<const V2*>(row + 2);
-                    const V2 ym2 = *reinterpret_cast<const V2*>(row - 2 * BX), ym1 = *reinterpret_cast<const V2*>(row - BX);
-                    const V2 yp1 = *reinterpret_cast<const V2*>(row + BX), yp2 = *reinterpret_cast<const V2*>(row + 2 * BX);
-                    if (a.iso) {
-                        const REAL c = a.kx / REAL(12);
-                        Lu.x = c * (-xl.x + REAL(16) * xl.y + REAL(16) * zc.y - xr.x
-                                    - ym2.x + REAL(16) * ym1.x - REAL(90) * zc.x + REAL(16) * yp1.x - yp2.x
-                                    - zm2.x + REAL(16) * zm1.x + REAL(16) * zp1.x - zp2.x);
-                        Lu.y = c * (-xl.y + REAL(16) * zc.x + REAL(16) * xr.x - xr.y
-                                    - ym2.y + REAL(16) * ym1.y - REAL(90) * zc.y + REAL(16) * yp1.y - yp2.y
-                                    - zm2.y + REAL(16) * zm1.y + REAL(16) * zp1.y - zp2.y);
-                    } else {
-                        Lu.x = a.kx * (-xl.x + REAL(16) * xl.y - REAL(30) * zc.x + REAL(16) * zc.y - xr.x) +
-                               a.ky * (-ym2.x + REAL(16) * ym1.x - REAL(30) * zc.x + REAL(16) * yp1.x - yp2.x) +
-                               a.kz * (-zm2.x + REAL(16) * zm1.x - REAL(30) * zc.x + REAL(16) * zp1.x - zp2.x);
-                        Lu.y = a.kx * (-xl.y + REAL(16) * zc.x - REAL(30) * zc.y + REAL(16) * xr.x - xr.y) +
-                               a.ky * (-ym2.y + REAL(16) * ym1.y - REAL(30) * zc.y + REAL(16) * yp1.y - yp2.y) +
-                               a.kz * (-zm2.y + REAL(16) * zm1.y - REAL(30) * zc.y + REAL(16) * zp1.y - zp2.y);
-                    }
-                    Lu.x = xl0 ? Lu.x : REAL(0);
-                    Lu.y = xl1 ? Lu.y : REAL(0);
-                }
-                const V2 qo = (STAGE == 1) ? zc : uo_k;
-                const REAL r0 = rk_combine<REAL>(STAGE, zc.x, qo.x, Lu.x, a.dt);
-                const REAL r1 = rk_combine<REAL>(STAGE, zc.y, qo.y, Lu.y, a.dt);
-                res.x = xr0 ? r0 : zc.x;
-                res.y = xr1 ? r1 : zc.y;
-            }
-            if (in_dom) *reinterpret_cast<V2*>(out + col + a.plane * k) = res;
-        }
-        __syncthreads();                                    // everybody is done with the oldest live plane
-        // plane p-2 (= k) is no longer needed once its output is written: refill its slot
-        if (leader && n >= 2) { const int pn = p - 2 + NST; if (pn <= p_last) issue(pn); }
-    }
-}
-
-
 // ---------------------------------------------------------------------------------------------
-// v3 ("tma, warp-specialised"): the TMA kernel as a producer/consumer pipeline.
+// heat3d_stage_tma: TMA-staged tiles, 2.5-D streaming along z, as a producer/consumer pipeline.
+//   A CTA owns a 64 x TY tile (two x-adjacent cells per consumer thread) and marches a chunk of z planes.
 //   - one producer warp (a single elected lane) keeps NST planes in flight: per plane ONE 3-D TMA box
 //     of u (tile + halo 2) and, for stages 2 and 3, one box of uo (tile only), both completing on the
 //     stage's `full` mbarrier; it refills a slot as soon as the consumers' `empty` mbarrier fires;
@@ -275,7 +146,7 @@ __device__ __forceinline__ void mbar_arrive_(unsigned bar)
 }
 
 template <typename REAL, int TY, int NST>
-struct HeatTma2Smem {
+struct HeatTmaSmem {
     static constexpr int TX = 64, H = 2;
     static constexpr int HX = (sizeof(REAL) == 8) ? 2 : 4;
     static constexpr int BX = TX + 2 * HX, BY = TY + 2 * H;
@@ -288,15 +159,15 @@ struct HeatTma2Smem {
 
 template <typename REAL, int TY, int NST, int STAGE>
 __global__ void __launch_bounds__(32 * (TY + 1))
-heat3d_stage_tma2(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_uo,
+heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_uo,
                   HeatArgs<REAL> a, int chunk, REAL* __restrict__ out)
 {
     typedef typename Vec2T<REAL>::type V2;
-    typedef HeatTma2Smem<REAL, TY, NST> S;
+    typedef HeatTmaSmem<REAL, TY, NST> S;
     constexpr int TX = S::TX, H = S::H, HX = S::HX, BX = S::BX, BY = S::BY;
     constexpr unsigned kBytesU = BX * BY * sizeof(REAL), kBytesO = TX * TY * sizeof(REAL);
-    extern __shared__ __align__(128) unsigned char heat2_smem_raw[];
-    S& sm = *reinterpret_cast<S*>(heat2_smem_raw);
+    extern __shared__ __align__(128) unsigned char heat_smem_raw[];
+    S& sm = *reinterpret_cast<S*>(heat_smem_raw);
 
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
