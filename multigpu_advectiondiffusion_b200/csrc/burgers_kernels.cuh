@@ -402,6 +402,24 @@ burgers3d_stage_ring(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u,
     if (!in_dom[0]) col0 = 0;
     const int own0 = (ty + H) * RP + tx + H;
     constexpr int CS = NW * RP;                        // slot offset between a thread's cells
+    // per-cell activity of the general body, packed once into a bit mask (4 bits per cell: x, y, z
+    // contribution active, j==2 scratch row) -- recomputing the index comparisons every plane costs
+    // issue slots the rim tiles do not have either
+    unsigned act = 0;
+    {
+        const bool i_in3 = (i >= 3 && i <= a.nx - 4);
+#pragma unroll
+        for (int c = 0; c < CPT; c++) {
+            const int j = j0 + ty + c * NW;
+            const bool j_in3 = (j >= 3 && j <= a.ny - 4);
+            const bool xa = (MODE == BMODE_MGPU) ? (j_in3 && i >= 2 && i <= a.nx - 4) : (i_in3 && j_in3);
+            const bool ya = (MODE == BMODE_MGPU) ? (i_in3 && j >= 2 && j <= a.ny - 4) : (i_in3 && j_in3);
+            const bool za = i_in3 && j_in3;
+            const bool row2 = (MODE == BMODE_MGPU) && j == 2 && ya;
+            act |= ((xa ? 1u : 0u) | (ya ? 2u : 0u) | (za ? 4u : 0u) | (row2 ? 8u : 0u)) << (4 * c);
+        }
+    }
+    const bool x_seed0 = (MODE == BMODE_MGPU) && i == 2;
 
     REAL st_own[CPT];
     auto fetch_own = [&](auto fast, int p) {
@@ -500,25 +518,22 @@ burgers3d_stage_ring(BurgersArgs<REAL> a, int chunk, const REAL* __restrict__ u,
                     out[o] = val;
                     if (PEER) a.out2[o + a.off2] = val;
                 } else {
-                    const int j = j0 + r;
-                    const bool i_in3 = (i >= 3 && i <= a.nx - 4), j_in3 = (j >= 3 && j <= a.ny - 4);
-                    const bool xa = (MODE == BMODE_MGPU) ? (j_in3 && i >= 2 && i <= a.nx - 4) : (i_in3 && j_in3);
-                    const bool ya = (MODE == BMODE_MGPU) ? (i_in3 && j >= 2 && j <= a.ny - 4) : (i_in3 && j_in3);
-                    const bool za = i_in3 && j_in3;
+                    const bool xa = (act >> (4 * c)) & 1u, ya = (act >> (4 * c)) & 2u, za = (act >> (4 * c)) & 4u;
+                    const bool row2 = (act >> (4 * c)) & 8u;
                     if (own_m) {
                         const REAL fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
                         REAL fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
-                        fu_old = ((MODE == BMODE_MGPU) && i == 2) ? REAL(0) : fu_old;
+                        fu_old = x_seed0 ? REAL(0) : fu_old;
                         const REAL gu = sm.hn_y[eb][r + 1][tx] + sm.hp_y[eb][r + 2][tx];
                         REAL gu_old = sm.hn_y[eb][r][tx] + sm.hp_y[eb][r + 1][tx];
-                        gu_old = ((MODE == BMODE_MGPU) && j == 2) ? REAL(0) : gu_old;
+                        gu_old = ((MODE == BMODE_MGPU) && (j0 + r == 2)) ? REAL(0) : gu_old;
                         Lu = xa ? -(fu - fu_old) * a.rdx6 : REAL(0);
                         Lu = ya ? Lu - (gu - gu_old) * a.rdy6 : Lu;
                     }
                     if (in_dom[c]) {
                         const bool rk = (MODE == BMODE_MGPU) ? true : (own_m && za);
                         if (own_m) {
-                            if ((MODE == BMODE_MGPU) && j == 2 && ya) {
+                            if (row2) {
                                 const long long ra = (long long)i + P * m;
                                 if (STAGE > 1) Lu += rowacc[ra];
                                 rowacc[ra] = Lu;
