@@ -38,6 +38,11 @@ void orc_ic_heat2d_sgpu_##S(REAL* u0, int nx, int ny, REAL dx, REAL dy); \
 void orc_ic_burgers3d_sgpu_##S(REAL* u0, int nx, int ny, int nz, REAL dx, REAL dy, REAL dz); \
 void orc_ic_burgers3d_mgpu_##S(REAL* u0, int nx, int ny, int nz, REAL dx, REAL dy, REAL dz); \
 void orc_ic_heat3d_mgpu_##S(REAL* u0, int nx, int ny, int nz); \
+int  orc_heat2d_mgpu_run_##S(REAL* u, int nx, int ny_phys, REAL L, REAL W, REAL K, int iters, double* dt_out, int* it_out, double* t_out); \
+void orc_burgers2d_mgpu_rhs_##S(const REAL* u, REAL* Lu, int nx, int NY, REAL dx, REAL dy); \
+int  orc_burgers2d_mgpu_run_##S(REAL* u, int nx, int ny_phys, REAL L, REAL W, REAL CFL, REAL tEnd, int max_steps, double* dt_out, double* it_out, double* t_out); \
+void orc_ic_heat2d_mgpu_##S(REAL* u0, int nx, int ny); \
+void orc_ic_burgers2d_mgpu_##S(REAL* u0, int nx, int ny, REAL dx, REAL dy); \
 void orc_slab_split_##S(const REAL* h_q, REAL* h_s_q, int n, int nx, int ny, int _Nz); \
 void orc_slab_merge_##S(const REAL* h_s_q, REAL* h_q, int n, int nx, int ny, int _Nz); \
 int  orc_save_binary_##S(const REAL* u, size_t n, const char* name);

@@ -163,6 +163,55 @@ def heat2d(u0, iters, C_=1.0, L=10, W=10):
     return u, dict(dt=dt.value)
 
 
+# ---------------------------------------------------------------- 2-D multi-GPU programs (y-slabs)
+def ic_heat2d_mgpu(nx, ny, dtype=np.float64):
+    """Padded (ny+6, nx) array."""
+    s, R = _sfx(dtype)
+    u = np.empty((ny + 6, nx), dtype)
+    f = getattr(lib(), "orc_ic_heat2d_mgpu_" + s)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    f.restype = None
+    f(_ptr(u), nx, ny + 6)
+    return u
+
+
+def ic_burgers2d_mgpu(nx, ny, L=2.0, W=2.0, dtype=np.float64):
+    """Padded (ny+6, nx) array; dy = W/(ny-1) with the PHYSICAL ny (main.c:58)."""
+    s, R = _sfx(dtype)
+    u = np.empty((ny + 6, nx), dtype)
+    f = getattr(lib(), "orc_ic_burgers2d_mgpu_" + s)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, R, R]
+    f.restype = None
+    T = np.dtype(dtype).type
+    f(_ptr(u), nx, ny + 6, T(L) / T(nx - 1), T(W) / T(ny - 1))
+    return u
+
+
+def heat2d_mgpu(u0, iters, K=1.0, L=2.0, W=2.0):
+    s, R = _sfx(u0.dtype)
+    u = np.array(u0, copy=True, order="C")
+    NY, nx = u.shape
+    f = getattr(lib(), "orc_heat2d_mgpu_run_" + s)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, R, R, R, C.c_int,
+                  C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)]
+    dt, it, t = C.c_double(), C.c_int(), C.c_double()
+    rc = f(_ptr(u), nx, NY - 6, L, W, K, iters, C.byref(dt), C.byref(it), C.byref(t))
+    assert rc == 0
+    return u, dict(dt=dt.value, it=it.value, t=t.value)
+
+
+def burgers2d_mgpu(u0, tEnd, CFL=0.4, L=2.0, W=2.0, max_steps=-1):
+    s, R = _sfx(u0.dtype)
+    u = np.array(u0, copy=True, order="C")
+    NY, nx = u.shape
+    f = getattr(lib(), "orc_burgers2d_mgpu_run_" + s)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, R, R, R, R, C.c_int] + [C.POINTER(C.c_double)] * 3
+    dt, it, t = C.c_double(), C.c_double(), C.c_double()
+    rc = f(_ptr(u), nx, NY - 6, L, W, CFL, tEnd, max_steps, C.byref(dt), C.byref(it), C.byref(t))
+    assert rc == 0
+    return u, dict(dt=dt.value, it=it.value, t=t.value)
+
+
 def slab_split(h_q, n, _Nz):
     s, R = _sfx(h_q.dtype)
     NZ, ny, nx = h_q.shape

@@ -150,3 +150,58 @@ def mgpu_save(u, path, which="mgpu_burgers3d"):
     NZ, ny, nx = u.shape
     lib.ref_save.argtypes = [_dp, C.c_uint, C.c_uint, C.c_uint, C.c_char_p]
     lib.ref_save(np.ascontiguousarray(u), nx, ny, NZ, path.encode())
+
+
+# ---- 2-D multi-GPU programs (y-slab, padded to Ny+6 rows) -------------------------------------------------
+def _mgpu2d_init(name, ic, nx, ny, L, W):
+    lib = _load(name)
+    u = np.empty((ny + 6, nx))
+    lib.ref_init.argtypes = [C.c_int] + [C.c_uint] * 2 + [C.c_double] * 2 + [_dp]
+    lib.ref_init(ic, nx, ny, L, W, u)
+    return u
+
+
+def mgpu_heat2d_init(nx, ny, L=2.0, W=2.0, ic=3):
+    return _mgpu2d_init("mgpu_heat2d", ic, nx, ny, L, W)
+
+
+def mgpu_burgers2d_init(nx, ny, L=2.0, W=2.0, ic=3):
+    return _mgpu2d_init("mgpu_burgers2d", ic, nx, ny, L, W)
+
+
+def mgpu_heat2d(u0, P, iters, K=1.0, L=2.0, W=2.0, block=(32, 32)):
+    """u0: padded (Ny+6, Nx).  block[1] >= 4 so the one-block-row boundary launches cover their window."""
+    lib = _load("mgpu_heat2d")
+    NY, nx = u0.shape
+    ny = NY - 6
+    assert ny % P == 0 and block[1] >= 4
+    out = np.empty_like(u0)
+    dt, it, t = C.c_double(), C.c_int(), C.c_double()
+    lib.ref_run.argtypes = ([C.c_int] + [C.c_double] * 3 + [C.c_uint] * 5 + [_dp, _dp] +
+                            [C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_double)])
+    rc = lib.ref_run(P, K, L, W, nx, ny, iters, *block, np.ascontiguousarray(u0), out,
+                     C.byref(dt), C.byref(it), C.byref(t))
+    assert rc == 0
+    return out, dict(dt=dt.value, it=it.value, t=t.value)
+
+
+def mgpu_burgers2d(u0, P, tEnd, CFL=0.4, L=2.0, W=2.0, block=(32, 32)):
+    lib = _load("mgpu_burgers2d")
+    NY, nx = u0.shape
+    ny = NY - 6
+    assert ny % P == 0
+    out = np.empty_like(u0)
+    dt, it, t = C.c_double(), C.c_double(), C.c_double()
+    lib.ref_run.argtypes = ([C.c_int] + [C.c_double] * 4 + [C.c_uint] * 4 + [_dp, _dp] +
+                            [C.POINTER(C.c_double)] * 3)
+    rc = lib.ref_run(P, tEnd, CFL, L, W, nx, ny, *block, np.ascontiguousarray(u0), out,
+                     C.byref(dt), C.byref(it), C.byref(t))
+    assert rc == 0
+    return out, dict(dt=dt.value, it=it.value, t=t.value)
+
+
+def mgpu2d_save(u, path, which="mgpu_burgers2d"):
+    lib = _load(which)
+    NY, nx = u.shape
+    lib.ref_save.argtypes = [_dp, C.c_uint, C.c_uint, C.c_char_p]
+    lib.ref_save(np.ascontiguousarray(u), nx, NY, path.encode())

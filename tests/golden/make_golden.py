@@ -29,6 +29,10 @@ CASES = {
     "heat3d_mgpu": dict(nx=16, ny=16, nz=64, L=2.0, W=2.0, H=2.0, K=1.0, iters=5, P=2),
     # SingleGPU/Diffusion2d
     "heat2d_sgpu": dict(nx=64, ny=48, L=10, W=10, C=1.0, iters=10),
+    # MultiGPU/Diffusion2d_Baseline (y-slabs, disc IC), P=2
+    "heat2d_mgpu": dict(nx=56, ny=48, L=2.0, W=2.0, K=1.0, iters=12, P=2),
+    # MultiGPU/Burgers2d_Baseline (y-slabs, WENO5-JS inviscid), P=2
+    "burgers2d_mgpu": dict(nx=60, ny=48, L=2.0, W=2.0, CFL=0.4, tEnd=0.2, P=2),
 }
 
 
@@ -76,6 +80,27 @@ def main():
     u1, dt = ref.sgpu_heat2d(u0, c["C"], c["L"], c["W"], c["iters"], block=(16, 16))
     out["heat2d_sgpu_ic"], out["heat2d_sgpu_out"] = u0, u1
     out["heat2d_sgpu_dt"] = np.array([dt])
+
+    c = CASES["heat2d_mgpu"]
+    u0 = ref.mgpu_heat2d_init(c["nx"], c["ny"], c["L"], c["W"])
+    u1, info = ref.mgpu_heat2d(u0, c["P"], c["iters"], c["K"], c["L"], c["W"])
+    for P in (1, 4):
+        assert np.array_equal(u1, ref.mgpu_heat2d(u0, P, c["iters"], c["K"], c["L"], c["W"])[0])
+    out["heat2d_mgpu_ic"], out["heat2d_mgpu_out"] = u0, u1
+    out["heat2d_mgpu_info"] = np.array([info["dt"], info["it"], info["t"]])
+
+    c = CASES["burgers2d_mgpu"]
+    u0 = ref.mgpu_burgers2d_init(c["nx"], c["ny"], c["L"], c["W"])
+    u1, info = ref.mgpu_burgers2d(u0, c["P"], c["tEnd"], c["CFL"], c["L"], c["W"])
+    for P in (1, 4):
+        assert np.array_equal(u1, ref.mgpu_burgers2d(u0, P, c["tEnd"], c["CFL"], c["L"], c["W"])[0])
+    out["burgers2d_mgpu_ic"], out["burgers2d_mgpu_out"] = u0, u1
+    out["burgers2d_mgpu_info"] = np.array([info["dt"], info["it"], info["t"]])
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "result.bin")
+        ref.mgpu2d_save(u1, p)
+        out["burgers2d_mgpu_result_bin_sha256"] = np.frombuffer(
+            hashlib.sha256(open(p, "rb").read()).digest(), dtype=np.uint8)
 
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_vectors.npz")
     np.savez_compressed(path, **out)

@@ -74,6 +74,23 @@ def test_heat2d_golden(golden, golden_cases):
     assert info["dt"] == golden["heat2d_sgpu_dt"][0]
 
 
+def test_2d_mgpu_golden(golden, golden_cases, tmp_path):
+    """MultiGPU/Diffusion2d_Baseline and MultiGPU/Burgers2d_Baseline (y-slabs)."""
+    c = golden_cases["heat2d_mgpu"]
+    assert np.array_equal(orc.ic_heat2d_mgpu(c["nx"], c["ny"]), golden["heat2d_mgpu_ic"])
+    out, info = orc.heat2d_mgpu(golden["heat2d_mgpu_ic"], c["iters"], c["K"], c["L"], c["W"])
+    assert np.array_equal(out, golden["heat2d_mgpu_out"])
+    assert np.array_equal(np.array([info["dt"], info["it"], info["t"]]), golden["heat2d_mgpu_info"])
+    c = golden_cases["burgers2d_mgpu"]
+    assert np.array_equal(orc.ic_burgers2d_mgpu(c["nx"], c["ny"], c["L"], c["W"]), golden["burgers2d_mgpu_ic"])
+    out, info = orc.burgers2d_mgpu(golden["burgers2d_mgpu_ic"], c["tEnd"], c["CFL"], c["L"], c["W"])
+    assert np.array_equal(out, golden["burgers2d_mgpu_out"])
+    assert np.array_equal(np.array([info["dt"], info["it"], info["t"]]), golden["burgers2d_mgpu_info"])
+    p = str(tmp_path / "result.bin")
+    orc.save_binary(out, p)
+    assert hashlib.sha256(open(p, "rb").read()).digest() == golden["burgers2d_mgpu_result_bin_sha256"].tobytes()
+
+
 def test_heat_analytic_soft_pin():
     """The reference's only numeric known answer for heat: the analytic Gaussian
     u=(t0/t)^{3/2} exp(-r^2/4t) used by every heat driver (heat3d.m:36,
@@ -171,3 +188,27 @@ def test_live_heat2d():
     r, dt = ref.sgpu_heat2d(u0, iters=12, block=(16, 16))
     o, oi = orc.heat2d(u0, 12)
     assert np.array_equal(r, o) and dt == oi["dt"]
+
+
+@needs_ref
+@pytest.mark.parametrize("shape,P,iters", [((48, 64), 1, 9), ((37, 40), 2, 7), ((80, 96), 4, 5)])
+def test_live_heat2d_mgpu(shape, P, iters):
+    nx, ny = shape
+    u0 = ref.mgpu_heat2d_init(nx, ny)
+    assert np.array_equal(u0, orc.ic_heat2d_mgpu(nx, ny))
+    u0 = u0 + np.random.default_rng(3).random(u0.shape)      # exercise every row/column of the footprint
+    r, ri = ref.mgpu_heat2d(u0, P, iters)
+    o, oi = orc.heat2d_mgpu(u0, iters)
+    assert np.array_equal(r, o) and ri == oi
+
+
+@needs_ref
+@pytest.mark.parametrize("shape,P,tEnd", [((48, 64), 1, 0.1), ((37, 40), 2, 0.12), ((80, 96), 4, 0.05)])
+def test_live_burgers2d_mgpu(shape, P, tEnd):
+    nx, ny = shape
+    u0 = ref.mgpu_burgers2d_init(nx, ny)
+    assert np.array_equal(u0, orc.ic_burgers2d_mgpu(nx, ny))
+    for ic in (u0, np.random.default_rng(4).random(u0.shape) - 0.3):
+        r, ri = ref.mgpu_burgers2d(ic, P, tEnd)
+        o, oi = orc.burgers2d_mgpu(ic, tEnd)
+        assert np.array_equal(r, o) and ri == oi
