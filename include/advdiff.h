@@ -68,7 +68,14 @@ enum {
     ADV_TARGET_BURGERS3D_SGPU = 4,
     /* MultiGPU/Burgers3d_Baseline: WENO5-JS inviscid, z-padded, RK on every cell, the
      * i=2 / j=2 pseudo-updates of the reference at np>=2 */
-    ADV_TARGET_BURGERS3D_MGPU = 5
+    ADV_TARGET_BURGERS3D_MGPU = 5,
+    /* MultiGPU/Diffusion2d_Baseline: y-slabs, y-padded by 3 rows at both ends (ny+6 rows), anisotropic
+     * 9-pt operator on columns [3,nx-4] and rows [2, ny+3) (Compute_Laplace's jstart-1 offset,
+     * Kernels.cu:144), dt factor 0.8, RK on every cell */
+    ADV_TARGET_HEAT2D_MGPU = 6,
+    /* MultiGPU/Burgers2d_Baseline: y-slabs, WENO5-JS inviscid, x sweep on cells [2,nx-4] with the flux at
+     * 2-1/2 taken as 0 (Kernels.cu:249), y sweep on columns [3,nx-4], RK on every cell */
+    ADV_TARGET_BURGERS2D_MGPU = 7
 };
 
 enum { ADV_F64 = 0, ADV_F32 = 1 };          /* the reference's USE_FLOAT switch */
@@ -88,7 +95,8 @@ typedef struct adv_desc {
     int    flags;           /* ADV_FLAG_* */
     int    device;          /* CUDA device ordinal of this rank */
     /* z-slab decomposition (MGPU targets only; 1/0 otherwise).  Rank r owns physical planes
-     * [r*nz/nranks, (r+1)*nz/nranks) and stores nz/nranks + 6 planes (main.c:64-66). */
+     * [r*nz/nranks, (r+1)*nz/nranks) and stores nz/nranks + 6 planes (main.c:64-66).  The two 2-D MGPU
+     * targets split y the same way: rows [r*ny/nranks, ...), ny/nranks + 6 stored rows. */
     int    nranks, rank;
     /* 128-byte NCCL unique id shared by all ranks (adv_comm_unique_id), ignored when nranks==1 */
     unsigned char comm_id[128];
@@ -110,7 +118,8 @@ int  adv_comm_unique_id(unsigned char id[128]);
 int  adv_create(const adv_desc* desc, adv_solver** out);
 int  adv_destroy(adv_solver* s);
 
-/* element counts: the rank-local host array (nx*ny*(nz/nranks+6) for MGPU, nx*ny*nz otherwise) */
+/* element counts: the rank-local host array (nx*ny*(nz/nranks+6) for 3-D MGPU, nx*(ny/nranks+6) for 2-D
+ * MGPU, nx*ny*nz otherwise) */
 size_t adv_local_elems(const adv_solver* s);
 /* fixed time step the reference driver would use (main.c:193 / main.cpp:58,130-133) */
 double adv_dt(const adv_solver* s);
@@ -187,7 +196,10 @@ typedef struct adv_stage_args {
  * (DiffusionMPICUDA.h:116-121) */
 int adv_heat3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* cuda_stream);
 int adv_heat3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* cuda_stream);
-/* replaces Call_Lu2d + Call_RK2d (diffusion2d.h:57-59); ny rows, nzs ignored */
+/* replaces Call_Lu2d + Call_RK2d (diffusion2d.h:57-59); ny rows, nzs ignored.  With
+ * ADV_TARGET_HEAT2D_MGPU it replaces Call_Diff_ + Call_sspRK of MultiGPU/Diffusion2d_Baseline
+ * (DiffusionMPICUDA.h:113-118): ny = STORED rows of the slab, [k_begin,k_end) = rows to produce,
+ * [own_lo,own_hi) = owned rows, k_global0 = global index of local row 0. */
 int adv_heat2d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* cuda_stream);
 int adv_heat2d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* cuda_stream);
 /* replaces Call_Adv_x/y/z + Call_Diff_ + Call_sspRK (Burgers.h:73-82) and
@@ -198,6 +210,12 @@ int adv_heat2d_stage_f32(const adv_stage_args* a, const float* u_in, const float
  * 2 and 3 read and update it; it may be NULL for the other targets. */
 int adv_burgers3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, double* rowacc, void* cuda_stream);
 int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, float* rowacc, void* cuda_stream);
+
+/* replaces Compute_Adv_x_Async + Compute_Adv_y_Async + Compute_sspRK3Async of MultiGPU/Burgers2d_Baseline
+ * (BurgersMPICUDA.h:118-127), target ADV_TARGET_BURGERS2D_MGPU: ny = STORED rows of the slab,
+ * [k_begin,k_end) = rows to produce, [own_lo,own_hi) = owned rows (3, ny-3); no scratch needed. */
+int adv_burgers2d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* cuda_stream);
+int adv_burgers2d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* cuda_stream);
 
 /* No counterpart in the reference.  adv_burgers3d_stage_f64 for ADV_TARGET_BURGERS3D_MGPU without the
  * rowacc argument: the scratch is a fixed array inside the library's device image, so this entry point

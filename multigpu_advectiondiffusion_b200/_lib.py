@@ -14,6 +14,8 @@ TARGETS = {
     "heat3d_mgpu": 3,
     "burgers3d_sgpu": 4,
     "burgers3d_mgpu": 5,
+    "heat2d_mgpu": 6,
+    "burgers2d_mgpu": 7,
 }
 F64, F32 = 0, 1
 FLAG_VISC_ONCE = 0x1
@@ -77,6 +79,8 @@ SIGNATURES = {
     "adv_heat3d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
     "adv_heat2d_stage_f64": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
     "adv_heat2d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
+    "adv_burgers2d_stage_f64": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
+    "adv_burgers2d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),
     "adv_burgers3d_stage_f64": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P, _P]),
     "adv_burgers3d_stage_f32": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P, _P]),
     "adv_burgers3d_stage_f64_noalloc": (C.c_int, [C.POINTER(StageArgs), _P, _P, _P, _P]),

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "burgers_kernels.cuh"
+#include "burgers2d_kernels.cuh"
 #include "common.cuh"
 #include "halo.cuh"
 #include "heat_kernels.cuh"
@@ -65,9 +66,11 @@ extern "C" int adv_device_count(int* count)
 static bool is_heat(int t)
 {
     return t == ADV_TARGET_HEAT2D_SGPU || t == ADV_TARGET_HEAT3D_SGPU_BASELINE ||
-           t == ADV_TARGET_HEAT3D_SGPU_BLOCKING || t == ADV_TARGET_HEAT3D_MGPU;
+           t == ADV_TARGET_HEAT3D_SGPU_BLOCKING || t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_HEAT2D_MGPU;
 }
-static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU; }
+// the two y-slab programs: the slab unit is one ROW (pitch elements), not one z-plane
+static bool is_2d_mgpu(int t) { return t == ADV_TARGET_HEAT2D_MGPU || t == ADV_TARGET_BURGERS2D_MGPU; }
+static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU || is_2d_mgpu(t); }
 
 // second destination of a stage launch (fused halo exchange); internal, not part of the public stage ABI
 struct PeerOut { void* out2; long long off2; };
@@ -112,6 +115,11 @@ static int heat_args_from(const adv_stage_args* a, HeatArgs<REAL>& h)
         h.lap = Box3{{3, 3, a->own_lo}, {nx - 4, ny - 4, a->own_hi - 1}};
         h.rk = Box3{{3, 3, 0}, {nx - 4, ny - 4, nz - 1}};
         h.iso = 1;
+        break;
+    case ADV_TARGET_HEAT2D_MGPU:            // MultiGPU/Diffusion2d_Baseline/Kernels.cu:144-151,170 (ny = stored rows)
+        // Compute_Laplace starts one row below its window (j = ... + jstart-1): on the first slab that is pad row 2
+        h.lap = Box3{{3, a->own_lo - (a->k_global0 == 0 ? 1 : 0), 0}, {nx - 4, a->own_hi - 1, 0}};
+        h.rk = Box3{{0, 0, 0}, {nx - 1, ny - 1, 0}};
         break;
     default:
         return fail(ADV_ERR_INVALID, "target %d is not a heat target", a->target);
@@ -213,18 +221,83 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
 }
 
 template <typename REAL>
-static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st, PeerOut peer = kNoPeer)
 {
     int rc = check_stage_args(a, u_in, uo, u_out, 7);
     if (rc) return rc;
+    const bool slab = a->target == ADV_TARGET_HEAT2D_MGPU;
+    if (slab && (a->k_begin < 0 || a->k_end > a->ny || a->k_begin > a->k_end)) return fail(ADV_ERR_INVALID, "bad row window [%d,%d) of %d", a->k_begin, a->k_end, a->ny);
+    if (slab && (a->own_lo < 3 || a->own_hi > a->ny - 3)) return fail(ADV_ERR_INVALID, "owned rows [%d,%d) need 3 rows of halo inside [0,%d)", a->own_lo, a->own_hi, a->ny);
     HeatArgs<REAL> h;
     adv_stage_args b = *a;
     b.nzs = 1; b.k_begin = 0; b.k_end = 1;
     rc = heat_args_from<REAL>(&b, h);
     if (rc) return rc;
-    dim3 block(32, 8, 1);
-    dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, 1);
-    heat2d_stage_direct<REAL><<<grid, block, 0, st>>>(h, u_in, a->stage == 1 ? u_in : uo, u_out);
+    h.kb = slab ? a->k_begin : 0; h.ke = slab ? a->k_end : a->ny;       // ROW window for the 2-D kernels
+    if (h.kb == h.ke) return ADV_OK;
+    h.out2 = (REAL*)peer.out2; h.off2 = peer.off2;
+    const size_t vb = 2 * sizeof(REAL);
+    const bool vec_ok = a->pitch % 2 == 0 && (uintptr_t)u_in % vb == 0 && (uintptr_t)u_out % vb == 0 && (a->stage == 1 || (uintptr_t)uo % vb == 0) &&
+                        (!peer.out2 || ((uintptr_t)peer.out2 % vb == 0 && peer.off2 % 2 == 0));
+    // pairs-of-cells row-marching kernel for slabs and large grids; one-thread-per-cell kernel for the small
+    // single-GPU case (512^2 lives in L2 and is launch-bound) and for unaligned caller buffers
+    if (vec_ok && (slab || (size_t)a->nx * a->ny > ((size_t)1 << 21))) {
+        const int rows = h.ke - h.kb, gx = (a->nx / 2 + 1 + 127) / 128;
+        int nch = (4 * 148 + gx - 1) / gx;                  // ~4 CTAs of 128 threads per SM ...
+        if (nch > rows / 16) nch = rows / 16;               // ... but chunks of >= 16 rows (4 rows of run-in each)
+        if (nch < 1) nch = 1;
+        const int chunk = (rows + nch - 1) / nch;
+        dim3 grid(gx, (rows + chunk - 1) / chunk, 1), block(128, 1, 1);
+        const REAL* uo_ = a->stage == 1 ? u_in : uo;
+#define LAUNCH_ROWS(STAGE_) do { \
+            if (peer.out2) heat2d_stage_rows<REAL, STAGE_, true><<<grid, block, 0, st>>>(h, chunk, u_in, uo_, u_out); \
+            else heat2d_stage_rows<REAL, STAGE_, false><<<grid, block, 0, st>>>(h, chunk, u_in, uo_, u_out); } while (0)
+        if (a->stage == 1) LAUNCH_ROWS(1); else if (a->stage == 2) LAUNCH_ROWS(2); else LAUNCH_ROWS(3);
+#undef LAUNCH_ROWS
+    } else {
+        dim3 block(32, 8, 1);
+        dim3 grid((a->nx + 31) / 32, (h.ke - h.kb + 7) / 8, 1);
+        heat2d_stage_direct<REAL><<<grid, block, 0, st>>>(h, u_in, a->stage == 1 ? u_in : uo, u_out);
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
+// Burgers 2-D y-slab stage (MultiGPU/Burgers2d_Baseline): ny = stored rows, [k_begin,k_end) = row window
+template <typename REAL>
+static int burgers2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st, PeerOut peer = kNoPeer)
+{
+    int rc = check_stage_args(a, u_in, uo, u_out, 8);
+    if (rc) return rc;
+    if (a->target != ADV_TARGET_BURGERS2D_MGPU) return fail(ADV_ERR_INVALID, "target %d is not the 2-D Burgers target", a->target);
+    if (a->k_begin < 0 || a->k_end > a->ny || a->k_begin > a->k_end) return fail(ADV_ERR_INVALID, "bad row window [%d,%d) of %d", a->k_begin, a->k_end, a->ny);
+    if (a->own_lo < 3 || a->own_hi > a->ny - 3) return fail(ADV_ERR_INVALID, "owned rows [%d,%d) need 3 rows of halo inside [0,%d)", a->own_lo, a->own_hi, a->ny);
+    if (a->k_begin == a->k_end) return ADV_OK;
+    BurgersArgs<REAL> b;
+    memset(&b, 0, sizeof(b));
+    b.nx = a->nx; b.ny = a->ny; b.nzs = 1;
+    b.pitch = (long long)a->pitch; b.plane = (long long)a->pitch * a->ny;
+    b.kb = a->k_begin; b.ke = a->k_end; b.own_lo = a->own_lo; b.own_hi = a->own_hi;
+    b.stage = a->stage;
+    b.dt = (REAL)a->dt; b.dx = (REAL)a->dx; b.dy = (REAL)a->dy;
+    b.rdx = REAL(1) / b.dx; b.rdy = REAL(1) / b.dy;
+    b.rdx6 = b.rdx / REAL(6); b.rdy6 = b.rdy / REAL(6);
+    b.out2 = (REAL*)peer.out2; b.off2 = peer.off2;
+    b.quirk_lo = 1; b.quirk_hi = 0;
+    fill_weno_consts<REAL>(b, WENO_JS);
+    constexpr int TX = 64, TY = 16, NT = 256;
+    dim3 grid((a->nx + TX - 1) / TX, (a->k_end - a->k_begin + TY - 1) / TY, 1), block(NT, 1, 1);
+    const REAL* uo_ = a->stage == 1 ? u_in : uo;
+    const size_t shm = sizeof(Burgers2dSmem<REAL, TX, TY>);
+#define LAUNCH_B2D(STAGE_, PEER_) do { \
+        auto kfn = burgers2d_stage_tile<REAL, WENO_JS, TX, TY, NT, STAGE_, PEER_>; \
+        CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
+        kfn<<<grid, block, shm, st>>>(b, u_in, uo_, u_out); } while (0)
+#define LAUNCH_B2D_S(PEER_) do { \
+        if (a->stage == 1) LAUNCH_B2D(1, PEER_); else if (a->stage == 2) LAUNCH_B2D(2, PEER_); else LAUNCH_B2D(3, PEER_); } while (0)
+    if (peer.out2) LAUNCH_B2D_S(true); else LAUNCH_B2D_S(false);
+#undef LAUNCH_B2D_S
+#undef LAUNCH_B2D
     CUDA_TRY(cudaGetLastError());
     return ADV_OK;
 }
@@ -301,6 +374,10 @@ extern "C" int adv_heat2d_stage_f64(const adv_stage_args* a, const double* u_in,
 { return heat2d_stage_impl<double>(a, u_in, uo, u_out, (cudaStream_t)st); }
 extern "C" int adv_heat2d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* st)
 { return heat2d_stage_impl<float>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_burgers2d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, void* st)
+{ return burgers2d_stage_impl<double>(a, u_in, uo, u_out, (cudaStream_t)st); }
+extern "C" int adv_burgers2d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, void* st)
+{ return burgers2d_stage_impl<float>(a, u_in, uo, u_out, (cudaStream_t)st); }
 extern "C" int adv_burgers3d_stage_f64(const adv_stage_args* a, const double* u_in, const double* uo, double* u_out, double* rowacc, void* st)
 { return burgers3d_stage_impl<double>(a, u_in, uo, u_out, rowacc, (cudaStream_t)st); }
 extern "C" int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_in, const float* uo, float* u_out, float* rowacc, void* st)
@@ -312,8 +389,10 @@ extern "C" int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_i
 struct adv_solver {
     adv_desc d;
     size_t esz;                 // sizeof(REAL)
-    int nzl;                    // physical planes owned by this rank
-    int nzs;                    // stored planes (nzl + 6 for MGPU targets)
+    int nzl;                    // physical slab units (z-planes; rows for the 2-D y-slab targets) owned by this rank
+    int nzs;                    // stored units (nzl + 6 for MGPU targets)
+    int urows;                  // rows per slab unit: ny for z-slabs, 1 for y-slabs
+    int nsplit;                 // physical extent along the split axis (nz, or ny for y-slabs)
     size_t pitch;               // elements
     size_t buf_bytes;
     void* buf[3];               // ping-pong field buffers; buf[cur] holds the solution
@@ -385,6 +464,16 @@ static void make_constants(adv_solver* s)
         dt = (REAL)d.coef * dx / 1.0;
         break;
     }
+    case ADV_TARGET_HEAT2D_MGPU: {          // MultiGPU/Diffusion2d_Baseline/main.c:57-62
+        C = (REAL)d.coef;
+        dt = 1 / (2 * C * (1 / dx / dx + 1 / dy / dy)) * 0.8;
+        kx = C / (12 * dx * dx); ky = C / (12 * dy * dy);
+        break;
+    }
+    case ADV_TARGET_BURGERS2D_MGPU: {       // MultiGPU/Burgers2d_Baseline/main.c:57-58,180
+        dt = (REAL)d.coef * dx / 1.0;
+        break;
+    }
     }
     s->dx = dx; s->dy = dy; s->dz = dz; s->dt_fixed = dt; s->kx = kx; s->ky = ky; s->kz = kz; s->visc_c = C;
 }
@@ -392,18 +481,21 @@ static void make_constants(adv_solver* s)
 static int validate_desc(const adv_desc* d)
 {
     if (!d) return fail(ADV_ERR_INVALID, "desc is NULL");
-    if (d->target < ADV_TARGET_HEAT2D_SGPU || d->target > ADV_TARGET_BURGERS3D_MGPU) return fail(ADV_ERR_INVALID, "unknown target %d", d->target);
+    if (d->target < ADV_TARGET_HEAT2D_SGPU || d->target > ADV_TARGET_BURGERS2D_MGPU) return fail(ADV_ERR_INVALID, "unknown target %d", d->target);
     if (d->precision != ADV_F64 && d->precision != ADV_F32) return fail(ADV_ERR_INVALID, "unknown precision %d", d->precision);
     const int minn = is_heat(d->target) ? 7 : 8;
     if (d->nx < minn || d->ny < minn) return fail(ADV_ERR_INVALID, "grid too small: %d x %d", d->nx, d->ny);
-    if (d->target != ADV_TARGET_HEAT2D_SGPU && d->nz < minn) return fail(ADV_ERR_INVALID, "grid too small: nz=%d", d->nz);
+    const bool two_d = d->target == ADV_TARGET_HEAT2D_SGPU || is_2d_mgpu(d->target);
+    if (!two_d && d->nz < minn) return fail(ADV_ERR_INVALID, "grid too small: nz=%d", d->nz);
     const int P = d->nranks <= 0 ? 1 : d->nranks;
-    if (P > 1 && !is_mgpu(d->target)) return fail(ADV_ERR_INVALID, "z-slab decomposition needs an MGPU target");
+    if (P > 1 && !is_mgpu(d->target)) return fail(ADV_ERR_INVALID, "slab decomposition needs an MGPU target");
     if (P > 1) {
         if (d->rank < 0 || d->rank >= P) return fail(ADV_ERR_INVALID, "rank %d outside [0,%d)", d->rank, P);
-        // the reference silently drops planes when Nz %% P != 0 (main.c:64); refuse instead
-        if (d->nz % P) return fail(ADV_ERR_INVALID, "nz=%d is not divisible by nranks=%d", d->nz, P);
-        if (d->nz / P < 2 * ADV_RADIUS) return fail(ADV_ERR_INVALID, "slab of %d planes is thinner than 2*RADIUS", d->nz / P);
+        // the reference silently drops planes (rows) when Nz %% P != 0 (main.c:64); refuse instead
+        const int n = is_2d_mgpu(d->target) ? d->ny : d->nz;
+        const char* ax = is_2d_mgpu(d->target) ? "ny" : "nz";
+        if (n % P) return fail(ADV_ERR_INVALID, "%s=%d is not divisible by nranks=%d", ax, n, P);
+        if (n / P < 2 * ADV_RADIUS) return fail(ADV_ERR_INVALID, "slab of %d %s is thinner than 2*RADIUS", n / P, is_2d_mgpu(d->target) ? "rows" : "planes");
     }
     if (!(d->coef > 0)) return fail(ADV_ERR_INVALID, "coef (C/K/CFL) must be positive");
     return ADV_OK;
@@ -429,13 +521,15 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
     memset((void*)s, 0, sizeof(*s));
     s->d = *desc;
     if (s->d.nranks <= 0) { s->d.nranks = 1; s->d.rank = 0; }
-    if (s->d.target == ADV_TARGET_HEAT2D_SGPU) s->d.nz = 1;
+    if (s->d.target == ADV_TARGET_HEAT2D_SGPU || is_2d_mgpu(s->d.target)) s->d.nz = 1;
     s->esz = desc->precision == ADV_F64 ? 8 : 4;
-    s->nzl = s->d.nz / s->d.nranks;
+    s->urows = is_2d_mgpu(s->d.target) ? 1 : s->d.ny;
+    s->nsplit = is_2d_mgpu(s->d.target) ? s->d.ny : s->d.nz;
+    s->nzl = s->nsplit / s->d.nranks;
     s->nzs = is_mgpu(desc->target) ? s->nzl + 2 * ADV_RADIUS : s->nzl;
     const size_t align = 128 / s->esz;                  // rows start on 128-byte lines
     s->pitch = ((size_t)desc->nx + align - 1) / align * align;
-    s->buf_bytes = s->pitch * (size_t)desc->ny * (size_t)s->nzs * s->esz;
+    s->buf_bytes = s->pitch * (size_t)s->urows * (size_t)s->nzs * s->esz;
     if (desc->precision == ADV_F64) make_constants<double>(s); else make_constants<float>(s);
 
 #define CREATE_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { \
@@ -492,7 +586,7 @@ extern "C" int adv_destroy(adv_solver* s)
     return ADV_OK;
 }
 
-extern "C" size_t adv_local_elems(const adv_solver* s) { return s ? (size_t)s->d.nx * s->d.ny * s->nzs : 0; }
+extern "C" size_t adv_local_elems(const adv_solver* s) { return s ? (size_t)s->d.nx * s->urows * s->nzs : 0; }
 extern "C" double adv_dt(const adv_solver* s) { return s ? s->dt_fixed : 0.0; }
 extern "C" long long adv_kernel_launches(const adv_solver* s) { return s ? s->launches : 0; }
 
@@ -501,7 +595,7 @@ extern "C" int adv_upload(adv_solver* s, const void* host)
     if (!s || !host) return fail(ADV_ERR_INVALID, "NULL argument");
     CUDA_TRY(cudaSetDevice(s->d.device));
     const size_t row = (size_t)s->d.nx * s->esz;
-    CUDA_TRY(cudaMemcpy2DAsync(s->buf[s->cur], s->pitch * s->esz, host, row, row, (size_t)s->d.ny * s->nzs,
+    CUDA_TRY(cudaMemcpy2DAsync(s->buf[s->cur], s->pitch * s->esz, host, row, row, (size_t)s->urows * s->nzs,
                                cudaMemcpyHostToDevice, s->stream));
     s->uploaded = true;
     return ADV_OK;
@@ -513,7 +607,7 @@ extern "C" int adv_download(adv_solver* s, void* host)
     if (!s->uploaded) return fail(ADV_ERR_STATE, "no field uploaded yet");
     CUDA_TRY(cudaSetDevice(s->d.device));
     const size_t row = (size_t)s->d.nx * s->esz;
-    CUDA_TRY(cudaMemcpy2DAsync(host, row, s->buf[s->cur], s->pitch * s->esz, row, (size_t)s->d.ny * s->nzs,
+    CUDA_TRY(cudaMemcpy2DAsync(host, row, s->buf[s->cur], s->pitch * s->esz, row, (size_t)s->urows * s->nzs,
                                cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     return ADV_OK;
@@ -551,9 +645,9 @@ template <typename REAL>
 static void reference_ic_local(const adv_solver* s, REAL* h)
 {
     const adv_desc& d = s->d;
-    const int nx = d.nx, ny = d.ny;
+    const int nx = d.nx, ny = s->urows;                                  // y-slab targets: one row per slab unit, k = global row
     const REAL dx = (REAL)s->dx, dy = (REAL)s->dy, dz = (REAL)s->dz;
-    const int NZ = is_mgpu(d.target) ? d.nz + 2 * ADV_RADIUS : d.nz;     // global stored planes
+    const int NZ = is_mgpu(d.target) ? s->nsplit + 2 * ADV_RADIUS : d.nz; // global stored planes (rows)
     const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;            // Init_subdomain, Tools.c:181-200
     for (int kl = 0; kl < s->nzs; kl++) {
         const int k = kl + kg0;
@@ -585,6 +679,15 @@ static void reference_ic_local(const adv_solver* s, REAL* h)
                     else v = 1.0 * exp(-(((0.5 * (nx - 1) - i) * dx * (0.5 * (nx - 1) - i) * dx) +
                                           ((0.5 * (ny - 1) - j) * dy * (0.5 * (ny - 1) - j) * dy) +
                                           ((0.5 * (NZ - 1) - k) * dz * (0.5 * (NZ - 1) - k) * dz)) / 0.1);
+                    break;
+                case ADV_TARGET_HEAT2D_MGPU:        // MultiGPU/Diffusion2d_Baseline/Tools.c:108-121 (radius rounded by sqrtf)
+                    v = (sqrtf((float)((i * 1. / (nx - 1) - 0.5) * (i * 1. / (nx - 1) - 0.5) +
+                                       (k * 1. / (NZ - 1) - 0.5) * (k * 1. / (NZ - 1) - 0.5))) < 0.2) ? 1.0 : 0.0;
+                    break;
+                case ADV_TARGET_BURGERS2D_MGPU:     // MultiGPU/Burgers2d_Baseline/Tools.c:108-121, BurgersMPICUDA.h:60
+                    if (i == 0 || i == nx - 1 || k == 0 || k == NZ - 1) v = 0.0;
+                    else v = 1.0 * exp(-(((0.5 * (nx - 1) - i) * dx * (0.5 * (nx - 1) - i) * dx) +
+                                          ((0.5 * (NZ - 1) - k) * dy * (0.5 * (NZ - 1) - k) * dy)) / 0.1);
                     break;
                 }
                 h[o] = v;
@@ -618,18 +721,24 @@ static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in
     adv_stage_args a;
     memset(&a, 0, sizeof(a));
     a.target = s->d.target; a.flags = s->d.flags; a.stage = stage;
-    a.nx = s->d.nx; a.ny = s->d.ny; a.nzs = s->nzs; a.pitch = s->pitch;
+    const bool yslab = is_2d_mgpu(s->d.target);
+    a.nx = s->d.nx; a.ny = yslab ? s->nzs : s->d.ny; a.nzs = yslab ? 1 : s->nzs; a.pitch = s->pitch;
     a.k_begin = kb; a.k_end = ke;
     a.own_lo = is_mgpu(s->d.target) ? ADV_RADIUS : 3;
     a.own_hi = s->nzs - 3;
-    a.k_global0 = 0;
+    a.k_global0 = yslab ? s->d.rank * s->nzl : 0;
     a.dt = dt; a.dx = s->dx; a.dy = s->dy; a.dz = s->dz; a.kx = s->kx; a.ky = s->ky; a.kz = s->kz;
     int rc;
     const bool f64 = s->esz == 8;
     switch (s->d.target) {
     case ADV_TARGET_HEAT2D_SGPU:
-        rc = f64 ? adv_heat2d_stage_f64(&a, (const double*)in, (const double*)uo, (double*)out, st)
-                 : adv_heat2d_stage_f32(&a, (const float*)in, (const float*)uo, (float*)out, st);
+    case ADV_TARGET_HEAT2D_MGPU:
+        rc = f64 ? heat2d_stage_impl<double>(&a, (const double*)in, (const double*)uo, (double*)out, st, peer)
+                 : heat2d_stage_impl<float>(&a, (const float*)in, (const float*)uo, (float*)out, st, peer);
+        break;
+    case ADV_TARGET_BURGERS2D_MGPU:
+        rc = f64 ? burgers2d_stage_impl<double>(&a, (const double*)in, (const double*)uo, (double*)out, st, peer)
+                 : burgers2d_stage_impl<float>(&a, (const float*)in, (const float*)uo, (float*)out, st, peer);
         break;
     case ADV_TARGET_BURGERS3D_SGPU:
     case ADV_TARGET_BURGERS3D_MGPU:
@@ -717,7 +826,7 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
     int ob = -1;
     for (int b = 0; b < 3; b++) if (s->buf[b] == out) ob = b;
     if (ob < 0) return fail(ADV_ERR_STATE, "stage output is not one of the solver's buffers");
-    const long long plane = (long long)s->pitch * s->d.ny;
+    const long long plane = (long long)s->pitch * s->urows;
     int rc;
     if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1))) return rc;
     if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1))) return rc;
@@ -754,7 +863,7 @@ static int do_stage(adv_solver* s, int stage, double dt, const void* in, const v
     if (r < P - 1) { rc = launch_stage(s, stage, dt, in, uo, out, s->nzs - 2 * R, s->nzs - R, s->stream); if (rc) return rc; }
     CUDA_TRY(cudaEventRecord(s->ev_boundary, s->stream));
     CUDA_TRY(cudaStreamWaitEvent(s->comm_stream, s->ev_boundary, 0));
-    rc = s->comm.exchange(out, s->pitch * (size_t)s->d.ny, s->nzs, s->esz, s->comm_stream, g_err, sizeof(g_err));
+    rc = s->comm.exchange(out, s->pitch * (size_t)s->urows, s->nzs, s->esz, s->comm_stream, g_err, sizeof(g_err));
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(s->ev_comm, s->comm_stream));
     // interior (and the global-end pad planes) while the slabs travel
@@ -783,7 +892,7 @@ extern "C" int adv_step(adv_solver* s, int nsteps)
     if (nsteps < 0) return fail(ADV_ERR_INVALID, "nsteps < 0");
     CUDA_TRY(cudaSetDevice(s->d.device));
     static const bool no_graph = getenv("ADV_NO_GRAPH") != nullptr;
-    const size_t cells = (size_t)s->d.nx * s->d.ny * s->nzs;
+    const size_t cells = (size_t)s->d.nx * s->urows * s->nzs;
     const bool use_graph = !no_graph && s->d.nranks == 1 && nsteps >= 12 && cells <= ((size_t)1 << 23);
     if (use_graph && !s->graph_exec) {
         // capture three steps starting from the current buffer assignment
@@ -863,7 +972,7 @@ extern "C" int adv_solve_host(const adv_desc* desc, const void* host_in, void* h
     int rc = adv_create(&d, &s);
     if (rc) return rc;
     rc = adv_upload(s, host_in);
-    const bool iters_mode = is_heat(d.target) && d.target != ADV_TARGET_HEAT3D_MGPU;
+    const bool iters_mode = is_heat(d.target) && !is_mgpu(d.target);
     if (!rc) {
         if (iters_mode) {
             rc = adv_step(s, (int)tEnd_or_iters);
@@ -878,7 +987,7 @@ extern "C" int adv_solve_host(const adv_desc* desc, const void* host_in, void* h
         if (is_mgpu(d.target)) {
             // Merge_domains (Tools.c:205-224): only owned planes are copied back; the six pad planes
             // of the output keep the values of the input.
-            const size_t n = adv_local_elems(s), xy = (size_t)d.nx * d.ny;
+            const size_t n = adv_local_elems(s), xy = (size_t)d.nx * s->urows;
             void* tmp = malloc(n * s->esz);
             if (!tmp) rc = fail(ADV_ERR_NOMEM, "out of host memory");
             if (!rc) rc = adv_download(s, tmp);

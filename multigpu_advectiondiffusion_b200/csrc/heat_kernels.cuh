@@ -65,8 +65,8 @@ heat2d_stage_direct(HeatArgs<REAL> a, const REAL* __restrict__ u, const REAL* __
                     REAL* __restrict__ out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = blockIdx.y * blockDim.y + threadIdx.y;
-    if (i >= a.nx || j >= a.ny) return;
+    const int j = a.kb + blockIdx.y * blockDim.y + threadIdx.y;       // rows [a.kb, a.ke) of this launch
+    if (i >= a.nx || j >= a.ke) return;
     const long long o = (long long)i + a.pitch * j;
     const REAL c = u[o];
     REAL res = c;
@@ -80,6 +80,7 @@ heat2d_stage_direct(HeatArgs<REAL> a, const REAL* __restrict__ u, const REAL* __
         res = rk_combine<REAL>(a.stage, c, qo, Lu, a.dt);
     }
     out[o] = res;
+    if (a.out2) a.out2[a.off2 + o] = res;
 }
 
 }  // namespace adv
@@ -97,6 +98,63 @@ __device__ __forceinline__ REAL rk_combine_fast(REAL q, REAL qo, REAL Lq, REAL d
     if (STAGE == 1) return qo + dt * Lq;
     if (STAGE == 2) return REAL(0.75) * qo + REAL(0.25) * (q + dt * Lq);
     return (qo + REAL(2) * (q + dt * Lq)) * REAL(1.0 / 3.0);
+}
+
+// 2-D, large grids and y-slabs (MultiGPU/Diffusion2d_Baseline/Kernels.cu:130-188): one thread per PAIR of
+// cells (one 16-byte access per row), marching a chunk of rows with a 5-deep register queue in y; the x
+// neighbours are the two adjacent aligned pairs, which the neighbouring lanes loaded two rows earlier (L1).
+// Rows [a.kb, a.ke) of `out` are produced; with PEER every produced row is also stored to out2 + off2.
+template <typename REAL> struct Pair2T;
+template <> struct Pair2T<double> { typedef double2 type; };
+template <> struct Pair2T<float> { typedef float2 type; };
+
+template <typename REAL, int STAGE, bool PEER>
+__global__ void __launch_bounds__(128)
+heat2d_stage_rows(HeatArgs<REAL> a, int chunk, const REAL* __restrict__ u, const REAL* __restrict__ uo,
+                  REAL* __restrict__ out)
+{
+    typedef typename Pair2T<REAL>::type V2;
+    const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int j0 = a.kb + blockIdx.y * chunk;
+    const int j1 = min(j0 + chunk, a.ke);
+    if (i >= a.nx || j0 >= j1) return;
+    const bool has1 = i + 1 < a.nx;
+    const bool lapx0 = i >= a.lap.lo[0] && i <= a.lap.hi[0], lapx1 = i + 1 >= a.lap.lo[0] && i + 1 <= a.lap.hi[0];
+    const bool rkx0 = i >= a.rk.lo[0] && i <= a.rk.hi[0], rkx1 = has1 && i + 1 >= a.rk.lo[0] && i + 1 <= a.rk.hi[0];
+    const bool ldl = i >= 2, ldr = (long long)i + 3 < a.pitch;
+    const V2 zero = {REAL(0), REAL(0)};
+    auto ld = [&](int j) -> V2 { return (j >= 0 && j < a.ny) ? *reinterpret_cast<const V2*>(u + (long long)i + a.pitch * j) : zero; };
+    V2 m2 = ld(j0 - 2), m1 = ld(j0 - 1), c = ld(j0), p1 = ld(j0 + 1), p2;
+    for (int j = j0; j < j1; j++) {
+        p2 = ld(j + 2);
+        const long long o = (long long)i + a.pitch * j;
+        const bool rky = j >= a.rk.lo[1] && j <= a.rk.hi[1];
+        const bool lapy = j >= a.lap.lo[1] && j <= a.lap.hi[1];
+        V2 res = c;
+        if (rky && (rkx0 || rkx1)) {
+            V2 Lu = zero;
+            if (lapy && (lapx0 || lapx1)) {
+                const V2 L = ldl ? *reinterpret_cast<const V2*>(u + o - 2) : zero;
+                const V2 R = ldr ? *reinterpret_cast<const V2*>(u + o + 2) : zero;
+                if (lapx0) Lu.x = a.kx * (-L.x + REAL(16) * L.y - REAL(30) * c.x + REAL(16) * c.y - R.x) +
+                                  a.ky * (-m2.x + REAL(16) * m1.x - REAL(30) * c.x + REAL(16) * p1.x - p2.x);
+                if (lapx1) Lu.y = a.kx * (-L.y + REAL(16) * c.x - REAL(30) * c.y + REAL(16) * R.x - R.y) +
+                                  a.ky * (-m2.y + REAL(16) * m1.y - REAL(30) * c.y + REAL(16) * p1.y - p2.y);
+            }
+            V2 qo = c;
+            if (STAGE != 1) qo = *reinterpret_cast<const V2*>(uo + o);
+            if (rkx0) res.x = rk_combine_fast<REAL, STAGE>(c.x, qo.x, Lu.x, a.dt);
+            if (rkx1) res.y = rk_combine_fast<REAL, STAGE>(c.y, qo.y, Lu.y, a.dt);
+        }
+        if (has1) {
+            *reinterpret_cast<V2*>(out + o) = res;
+            if (PEER) *reinterpret_cast<V2*>(a.out2 + a.off2 + o) = res;
+        } else {
+            out[o] = res.x;
+            if (PEER) a.out2[a.off2 + o] = res.x;
+        }
+        m2 = m1; m1 = c; c = p1; p1 = p2;
+    }
 }
 
 template <typename REAL> struct Vec2T;

@@ -8,6 +8,7 @@ import numpy as np
 from ._lib import Desc, F32, F64, TARGETS, check, lib
 
 _MGPU = ("heat3d_mgpu", "burgers3d_mgpu")
+_MGPU_2D = ("heat2d_mgpu", "burgers2d_mgpu")
 
 
 def _np_dtype(precision):
@@ -46,7 +47,12 @@ class Solver:
         check(lib().adv_create(C.byref(self.desc), C.byref(self._h)))
         self.nx, self.ny = nx, ny
         n = lib().adv_local_elems(self._h)
-        self.local_shape = (n // (nx * ny), ny, nx) if target != "heat2d_sgpu" else (ny, nx)
+        if target == "heat2d_sgpu":
+            self.local_shape = (ny, nx)
+        elif target in _MGPU_2D:
+            self.local_shape = (n // nx, nx)        # y-slab: ny/nranks + 6 stored rows
+        else:
+            self.local_shape = (n // (nx * ny), ny, nx)
 
     # -- lifetime
     def close(self):
@@ -133,6 +139,9 @@ def solve_host(target, u0, tEnd_or_iters, **kw):
     if target == "heat2d_sgpu":
         ny, nx = u0.shape
         nz = 1
+    elif target in _MGPU_2D:
+        nys, nx = u0.shape
+        ny, nz = nys - 6, 1
     else:
         nzs, ny, nx = u0.shape
         nz = nzs - 6 if target in _MGPU else nzs

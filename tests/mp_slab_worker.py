@@ -84,6 +84,44 @@ def run_cpu(rank, P, nx, ny, nz, nsteps):
         print("MP_OK cpu P=%d bit-exact vs oracle" % P)
 
 
+def run_cpu2d(rank, P, nx, ny, nsteps):
+    """y-slab analogue for MultiGPU/Burgers2d_Baseline: rows instead of planes, same exchange indices."""
+    L = orc.lib()
+    L.orc_burgers2d_mgpu_rhs_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_double]
+    L.orc_burgers2d_mgpu_rhs_f64.restype = None
+    g = orc.ic_burgers2d_mgpu(nx, ny)
+    dx, dy = 2.0 / (nx - 1), 2.0 / (ny - 1)
+    dt = 0.4 * dx
+    g0, g1 = slab_bounds(ny, P, rank)
+    u = g[g0:g1].copy()
+    nys = u.shape[0]
+    Lu = np.zeros_like(u)                      # zeroed once (main.c:172)
+    for _ in range(nsteps):
+        uo = u.copy()
+        for stage in (1, 2, 3):
+            L.orc_burgers2d_mgpu_rhs_f64(u.ctypes.data, Lu.ctypes.data, nx, nys, dx, dy)
+            if stage == 1:
+                new = uo + dt * Lu
+            elif stage == 2:
+                new = 0.75 * uo + 0.25 * (u + dt * Lu)
+            else:
+                new = (uo + 2 * (u + dt * Lu)) / 3
+            lo = 0 if rank == 0 else 3
+            hi = nys if rank == P - 1 else nys - 3
+            u[lo:hi] = new[lo:hi]
+            exchange_cpu(u, rank, P)
+    parts = [None] * P if rank == 0 else None
+    dist.gather_object(u, parts, dst=0)
+    if rank == 0:
+        merged = g.copy()
+        nyl = ny // P
+        for r in range(P):
+            merged[r * nyl + 3: r * nyl + 3 + nyl] = parts[r][3:3 + nyl]
+        want, _ = orc.burgers2d_mgpu(g, 1e9, max_steps=nsteps)
+        assert np.array_equal(merged, want), float(np.abs(merged - want).max())
+        print("MP_OK cpu2d P=%d bit-exact vs oracle" % P)
+
+
 def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
     import multigpu_advectiondiffusion_b200 as adv
     torch.cuda.set_device(rank)
@@ -94,9 +132,15 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         idb = [bytes(buf)]
     dist.broadcast_object_list(idb, 0)
     coef = 0.3 if "burgers" in target else 1.0
-    g = orc.ic_burgers3d_mgpu(nx, ny, nz) if "burgers" in target else orc.ic_heat3d_mgpu(nx, ny, nz)
+    two_d = "2d" in target
+    if two_d:       # y-slabs: the split axis is y, arrays are (ny+6, nx)
+        g = orc.ic_burgers2d_mgpu(nx, ny) if "burgers" in target else orc.ic_heat2d_mgpu(nx, ny)
+        nz = ny
+    else:
+        g = orc.ic_burgers3d_mgpu(nx, ny, nz) if "burgers" in target else orc.ic_heat3d_mgpu(nx, ny, nz)
     g0, g1 = slab_bounds(nz, P, rank)
-    with adv.Solver(target, nx, ny, nz, coef=coef, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
+    nz_arg = 1 if two_d else nz
+    with adv.Solver(target, nx, ny, nz_arg, coef=coef, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
         if halo == "peer":
             hs = [None] * P
             dist.all_gather_object(hs, s.peer_handle())
@@ -115,13 +159,18 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         nzl = nz // P
         for r in range(P):
             merged[r * nzl + 3: r * nzl + 3 + nzl] = parts[r][3:3 + nzl]
-        with adv.Solver(target, nx, ny, nz, coef=coef, device=0) as s1:
+        with adv.Solver(target, nx, ny, nz_arg, coef=coef, device=0) as s1:
             s1.upload(g)
             s1.step(nsteps)
             one = s1.download()
         one[:3], one[-3:] = g[:3], g[-3:]
         assert np.array_equal(merged, one), "P=%d differs from P=1 on the GPU: %g" % (P, float(np.abs(merged - one).max()))
-        if "burgers" in target:
+        if target == "burgers2d_mgpu":
+            want, _ = orc.burgers2d_mgpu(g, 1e9, CFL=coef, max_steps=nsteps)
+        elif target == "heat2d_mgpu":
+            want, wi = orc.heat2d_mgpu(g, nsteps)
+            assert wi["it"] == nsteps
+        elif "burgers" in target:
             want, _ = orc.burgers3d_mgpu(g, 1e9, max_steps=nsteps)
         else:
             want, _ = orc.heat3d(g, nsteps, "mgpu", L=2.0, W=2.0, H=2.0)
@@ -138,9 +187,11 @@ def main():
     try:
         if mode == "cpu":
             run_cpu(rank, P, 20, 22, 24, 2)
+            run_cpu2d(rank, P, 30, 48, 3)
         else:
             for halo in ("nccl", "peer"):
-                for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5)):
+                for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5),
+                                             ("burgers2d_mgpu", (72, 96, 1), 3), ("heat2d_mgpu", (70, 96, 1), 5)):
                     run_gpu(rank, P, target, *shape, steps, halo=halo)
     finally:
         dist.barrier()

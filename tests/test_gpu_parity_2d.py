@@ -1,0 +1,144 @@
+"""GPU parity for the two y-slab programs (MultiGPU/Diffusion2d_Baseline, MultiGPU/Burgers2d_Baseline),
+through the C ABI, against the committed outputs of the reference's own kernels and against the CPU
+oracle.  Tolerances as in test_gpu_parity.py: 1e-12 (double), 1e-5 (float), whole padded array."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import multigpu_advectiondiffusion_b200 as adv
+from multigpu_advectiondiffusion_b200 import _lib
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+TOL64 = 1e-12
+TOL32 = 1e-5
+rel = orc.rel_err
+
+
+def test_golden_heat2d_mgpu(golden, golden_cases):
+    c = golden_cases["heat2d_mgpu"]
+    dt = golden["heat2d_mgpu_info"][0]
+    out, info = adv.solve_host("heat2d_mgpu", golden["heat2d_mgpu_ic"], dt * c["iters"], lx=c["L"], ly=c["W"], coef=c["K"])
+    assert [info["dt"], info["it"], info["t"]] == list(golden["heat2d_mgpu_info"])
+    assert rel(out, golden["heat2d_mgpu_out"]) <= TOL64
+    assert np.array_equal(out[:3], golden["heat2d_mgpu_ic"][:3]) and np.array_equal(out[-3:], golden["heat2d_mgpu_ic"][-3:])
+
+
+def test_golden_burgers2d_mgpu(golden, golden_cases):
+    c = golden_cases["burgers2d_mgpu"]
+    out, info = adv.solve_host("burgers2d_mgpu", golden["burgers2d_mgpu_ic"], c["tEnd"], lx=c["L"], ly=c["W"], coef=c["CFL"])
+    assert [info["dt"], info["it"], info["t"]] == list(golden["burgers2d_mgpu_info"])
+    assert rel(out, golden["burgers2d_mgpu_out"]) <= TOL64
+    assert np.array_equal(out[:3], golden["burgers2d_mgpu_ic"][:3]) and np.array_equal(out[-3:], golden["burgers2d_mgpu_ic"][-3:])
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (400, 400), (131, 77), (33, 260), (1030, 48)])
+def test_heat2d_mgpu_vs_oracle(shape):
+    nx, ny = shape
+    # disc IC plus noise so that every row and column of the update footprint (pad row 2 included) matters
+    u0 = orc.ic_heat2d_mgpu(nx, ny) + np.random.default_rng(5).random((ny + 6, nx))
+    want, wi = orc.heat2d_mgpu(u0, 25)
+    got, gi = adv.solve_host("heat2d_mgpu", u0, wi["dt"] * 25, coef=1.0)
+    assert gi["it"] == wi["it"] and gi["dt"] == wi["dt"]
+    assert rel(got, want) <= TOL64
+
+
+@pytest.mark.parametrize("shape", [(64, 64, 2.0), (400, 400, 2.0), (131, 77, 1.2), (33, 260, 16.0), (1030, 48, 0.1)])
+def test_burgers2d_mgpu_vs_oracle(shape):
+    nx, ny, W = shape           # W keeps dy ~ dx so that dt = CFL*dx is stable in y too
+    for u0 in (orc.ic_burgers2d_mgpu(nx, ny, W=W), np.random.default_rng(6).random((ny + 6, nx)) - 0.3):
+        want, wi = orc.burgers2d_mgpu(u0, 1e9, W=W, max_steps=8)
+        assert np.isfinite(want).all()
+        with adv.Solver("burgers2d_mgpu", nx, ny, coef=0.4, ly=W) as s:
+            s.upload(u0)
+            s.step(8)
+            got = s.download()
+        got[:3], got[-3:] = u0[:3], u0[-3:]
+        assert rel(got, want) <= TOL64
+
+
+def test_2d_float_paths_vs_oracle():
+    u0 = orc.ic_burgers2d_mgpu(96, 80, dtype=np.float32)
+    want, _ = orc.burgers2d_mgpu(u0, 0.1)
+    got, _ = adv.solve_host("burgers2d_mgpu", u0, 0.1, coef=0.4, precision=adv.F32)
+    assert got.dtype == np.float32 and rel(got, want) <= TOL32
+    h0 = orc.ic_heat2d_mgpu(96, 80, dtype=np.float32)
+    want, wi = orc.heat2d_mgpu(h0, 20)
+    got, gi = adv.solve_host("heat2d_mgpu", h0, np.float32(wi["dt"]) * np.float32(20), coef=1.0, precision=adv.F32)
+    assert gi["it"] == wi["it"] and rel(got, want) <= TOL32
+
+
+def test_2d_reference_ic_generated_by_the_library_is_bit_exact():
+    for target, ic in (("heat2d_mgpu", orc.ic_heat2d_mgpu), ("burgers2d_mgpu", orc.ic_burgers2d_mgpu)):
+        with adv.Solver(target, 52, 44, coef=0.4) as s:
+            s.init_reference_ic()
+            assert np.array_equal(s.download(), ic(52, 44)), target
+
+
+@pytest.mark.parametrize("target", ["burgers2d_mgpu", "heat2d_mgpu"])
+def test_2d_stage_entry_points_split_row_windows(target):
+    """adv_burgers2d_stage_f64 / adv_heat2d_stage_f64 on caller-owned device memory: one step assembled from
+    stage calls == the oracle's step, and split row windows are bit-identical to one window."""
+    import torch
+    nx, ny = 100, 64
+    NY = ny + 6
+    rng = np.random.default_rng(8)
+    u0 = rng.random((NY, nx)) - 0.3
+    dx, dy = 2.0 / (nx - 1), 2.0 / (ny - 1)
+    if target == "burgers2d_mgpu":
+        dt, kx, ky = 0.4 * dx, 0.0, 0.0
+        want, _ = orc.burgers2d_mgpu(u0, 1e9, max_steps=1)
+        fn = adv.lib().adv_burgers2d_stage_f64
+    else:
+        dt = 1 / (2 * 1.0 * (1 / dx / dx + 1 / dy / dy)) * 0.8
+        kx, ky = 1.0 / (12 * dx * dx), 1.0 / (12 * dy * dy)
+        want, wi = orc.heat2d_mgpu(u0, 1)
+        assert wi["it"] == 1
+        fn = adv.lib().adv_heat2d_stage_f64
+    dev = torch.device("cuda:0")
+    A = torch.from_numpy(u0).to(dev)
+    results = []
+    for windows in ([(0, NY)], [(0, 3), (3, 6), (6, 23), (23, NY - 6), (NY - 6, NY - 3), (NY - 3, NY)]):
+        B, Cc = torch.empty_like(A), torch.empty_like(A)
+        st = torch.cuda.current_stream().cuda_stream
+        for stage, (src, dst) in enumerate(((A, B), (B, Cc), (Cc, B)), start=1):
+            for jb, je in windows:
+                a = _lib.StageArgs(target=adv.TARGETS[target], flags=0, stage=stage, nx=nx, ny=NY, nzs=1, pitch=nx,
+                                   k_begin=jb, k_end=je, own_lo=3, own_hi=NY - 3, k_global0=0,
+                                   dt=dt, dx=dx, dy=dy, dz=0, kx=kx, ky=ky, kz=0)
+                _lib.check(fn(C.byref(a), src.data_ptr(), A.data_ptr(), dst.data_ptr(), st))
+        torch.cuda.synchronize()
+        results.append(B.cpu().numpy())
+    assert np.array_equal(results[0], results[1])
+    got = results[0].copy()
+    got[:3], got[-3:] = u0[:3], u0[-3:]
+    assert rel(got, want) <= TOL64
+
+
+def test_2d_bad_arguments():
+    with pytest.raises(adv.AdvError) as e:
+        adv.Solver("burgers2d_mgpu", 64, 50, nranks=4, rank=0, coef=0.4)      # 50 rows do not split into 4
+    assert e.value.code == 1 and "divisible" in str(e.value)
+    with pytest.raises(adv.AdvError):
+        adv.Solver("heat2d_mgpu", 64, 16, nranks=4, rank=1, coef=1.0)         # 4-row slabs are thinner than 2*RADIUS
+
+
+def test_2d_large_grid_properties():
+    """4096^2 Burgers and heat: P=1 GPU runs at a size the oracle also finishes (a few seconds per step
+    count), plus boundedness (WENO keeps the Gaussian in [0, 1] up to overshoot 1e-3)."""
+    nx = ny = 2048
+    u0 = orc.ic_burgers2d_mgpu(nx, ny)
+    want, _ = orc.burgers2d_mgpu(u0, 1e9, max_steps=3)
+    with adv.Solver("burgers2d_mgpu", nx, ny, coef=0.4) as s:
+        s.upload(u0)
+        s.step(3)
+        got = s.download()
+    got[:3], got[-3:] = u0[:3], u0[-3:]
+    assert rel(got, want) <= TOL64
+    assert got.min() > -1e-3 and got.max() < 1 + 1e-3
+    h0 = orc.ic_heat2d_mgpu(nx, ny)
+    want, wi = orc.heat2d_mgpu(h0, 5)
+    got, gi = adv.solve_host("heat2d_mgpu", h0, wi["dt"] * 5, coef=1.0)
+    assert gi["it"] == wi["it"] and rel(got, want) <= TOL64

@@ -20,12 +20,12 @@ def _launch(mode, nproc, port):
 
 def test_cpu_gloo_two_ranks():
     r = _launch("cpu", 2, 29731)
-    assert r.returncode == 0 and "MP_OK cpu P=2" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.returncode == 0 and "MP_OK cpu P=2" in r.stdout and "MP_OK cpu2d P=2" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_cpu_gloo_four_ranks():
     r = _launch("cpu", 4, 29732)
-    assert r.returncode == 0 and "MP_OK cpu P=4" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.returncode == 0 and "MP_OK cpu P=4" in r.stdout and "MP_OK cpu2d P=4" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 @pytest.mark.gpu
@@ -34,7 +34,7 @@ def test_gpu_nccl_two_ranks():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
     r = _launch("gpu", 2, 29733)
-    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 4 and r.stdout.count("halo=peer") == 2, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 8 and r.stdout.count("halo=peer") == 4, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 @pytest.mark.gpu
@@ -44,4 +44,4 @@ def test_gpu_four_ranks_both_halo_modes():
     if torch.cuda.device_count() < 4:
         pytest.skip("needs 4 GPUs (run under gpurun --gpus 4)")
     r = _launch("gpu", 4, 29734)
-    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 4 and r.stdout.count("halo=peer") == 2, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu") == 8 and r.stdout.count("halo=peer") == 4, r.stdout[-3000:] + r.stderr[-3000:]
