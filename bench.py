@@ -38,6 +38,9 @@ WORKLOADS = {
     "heat3d_weak512": dict(target="heat3d_mgpu", n=(512, 512, 512), scaling="weak", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
     "heat3d_strong1024": dict(target="heat3d_mgpu", n=(1024, 1024, 1024), scaling="strong", L=(2.0, 2.0, 2.0), coef=1.0, e2e_steps=50),
     "heat2d_512": dict(target="heat2d_sgpu", n=(512, 512, 1), scaling="replicas", L=(10, 10, 1), coef=1.0, e2e_steps=1000),
+    # the two y-slab programs (MultiGPU/Burgers2d_Baseline, MultiGPU/Diffusion2d_Baseline); n = (nx, rows per GPU, 1)
+    "burgers2d_weak8192": dict(target="burgers2d_mgpu", n=(8192, 8192, 1), scaling="weak", L=(2.0, 2.0, 1), coef=0.4, e2e_steps=50),
+    "heat2d_weak8192": dict(target="heat2d_mgpu", n=(8192, 8192, 1), scaling="weak", L=(2.0, 2.0, 1), coef=1.0, e2e_steps=100),
     "heat3d_sgpu_256": dict(target="heat3d_sgpu_baseline", n=(256, 256, 256), scaling="replicas", L=(10, 10, 10), coef=1.0, e2e_steps=100),
 }
 BYTES_PER_CELL_STEP = {8: 64.0, 4: 32.0}     # 16 + 24 + 24, per time step
@@ -144,6 +147,20 @@ def cpu_sample(w, precision_bytes, target_seconds=12.0):
             f(u.ctypes.data, uo.ctypes.data, Lu.ctypes.data, nx, ny, planes, 1.0, 1.0, 1.0, 1e-6, 2)
         return time.perf_counter() - t0
 
+    if w["target"] in ("heat2d_mgpu", "burgers2d_mgpu"):
+        rows = 2048                                    # full row length, a bounded number of rows
+        if w["target"] == "burgers2d_mgpu":
+            u0, steps = orc.ic_burgers2d_mgpu(nx, rows, W=2.0 * rows / nx), 4
+            fn = lambda: orc.burgers2d_mgpu(u0, 1e9, W=2.0 * rows / nx, max_steps=steps)
+        else:
+            u0, steps = orc.ic_heat2d_mgpu(nx, rows), 20
+            fn = lambda: orc.heat2d_mgpu(u0, steps, W=2.0 * rows / nx)
+        fn()
+        t0 = time.perf_counter()
+        fn()
+        t = time.perf_counter() - t0
+        return {"value": nx * rows * 3 * steps / t / 1e6, "unit": "Mcell-updates/s", "cores": threads, "kind": "port",
+                "sample": "%d x %d rows of the workload, %d time steps, oracle/advdiff_oracle.c with OpenMP" % (nx, rows, steps), "seconds": t}
     if w["target"] == "heat2d_sgpu":
         u0 = orc.ic_heat2d_sgpu(nx, ny)
         steps = 300
@@ -186,14 +203,19 @@ def main():
     N = args.gpus
     esz = 8 if args.precision == "f64" else 4
     nx, ny, nz0 = w["n"]
-    nz_total = nz0 * N if w["scaling"] == "weak" else nz0
+    two_d = w["target"] in ("heat2d_mgpu", "burgers2d_mgpu")        # y-slabs: the split axis is y
+    if two_d:
+        ny = ny * N if w["scaling"] == "weak" else ny
+    nz_total = nz0 * N if w["scaling"] == "weak" and not two_d else nz0
     if w["scaling"] == "replicas":
         nz_total = nz0
     lz = w["L"][2] * (N if w["scaling"] == "weak" else 1)
+    ly = w["L"][1] * (N if two_d and w["scaling"] == "weak" else 1)
     config = {"workload": args.workload, "target": w["target"], "grid": [nx, ny, nz_total], "precision": args.precision,
-              "scheme": "WENO5-JS + Lax-Friedrichs + SSP-RK3" if "burgers" in w["target"] else "O4 13-pt Laplacian + SSP-RK3",
-              "decomposition": "z-slab x%d" % N if N > 1 else "single GPU",
-              "l2_policy": "no flush: working set 3 x %.2f GiB per GPU >> 126 MB L2" % (nx * ny * (nz_total / max(N, 1) + 6) * esz / 2**30)}
+              "scheme": "WENO5-JS + Lax-Friedrichs + SSP-RK3" if "burgers" in w["target"] else "O4 %s Laplacian + SSP-RK3" % ("9-pt" if two_d else "13-pt"),
+              "decomposition": ("%s-slab x%d" % ("y" if two_d else "z", N)) if N > 1 else "single GPU",
+              "l2_policy": "no flush: working set 3 x %.2f GiB per GPU >> 126 MB L2" %
+                           ((nx * (ny / max(N, 1) + 6) if two_d else nx * ny * (nz_total / max(N, 1) + 6)) * esz / 2**30)}
 
     # ---------------------------------------------------------------- reference arm (CPU)
     if args.impl == "reference":
@@ -206,7 +228,7 @@ def main():
             vals.append(cb["value"])
         v = max(vals)
         cb["value"] = v
-        line = {"impl": "reference", "metric": "Mcell-updates/s (3D %s, SSP-RK3)" % ("WENO5 Burgers" if "burgers" in w["target"] else "heat"),
+        line = {"impl": "reference", "metric": "Mcell-updates/s (%s %s, SSP-RK3)" % ("2D" if two_d or w["target"] == "heat2d_sgpu" else "3D", "WENO5 Burgers" if "burgers" in w["target"] else "heat"),
                 "value": v, "unit": "Mcell-updates/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": 1e3 * cb["seconds"], "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic", "config": config, "cpu_baseline": cb,
@@ -244,7 +266,7 @@ def main():
 
     if w["target"] == "heat2d_sgpu":
         config["l2_policy"] = "L2-resident by nature: 3 x 2 MiB field (launch-latency bound, SURVEY 8a2)"
-    s = adv.Solver(w["target"], nx, ny, nz_total, lx=w["L"][0], ly=w["L"][1], lz=lz, coef=w["coef"],
+    s = adv.Solver(w["target"], nx, ny, nz_total, lx=w["L"][0], ly=ly, lz=lz, coef=w["coef"],
                    precision=adv.F64 if esz == 8 else adv.F32, device=dev, nranks=nranks, rank=rank if nranks > 1 else 0,
                    comm_id=comm_id)
     if nranks > 1 and args.halo == "peer":
@@ -253,7 +275,7 @@ def main():
         s.peer_connect(hs[rank - 1] if rank > 0 else None, hs[rank + 1] if rank < nranks - 1 else None)
     config["halo"] = s.halo_mode
     s.init_reference_ic()
-    cells_local = nx * ny * (nz_total // nranks)
+    cells_local = nx * (ny // nranks) if two_d else nx * ny * (nz_total // nranks)
     cells_job = cells_local * (world if w["scaling"] == "replicas" or nranks > 1 else 1)
 
     def barrier():
@@ -289,7 +311,8 @@ def main():
     prof, fp64_peak = ncu_profile(args.workload)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": prof["dram_bytes_per_launch_mean"] if prof else None, "peak_source": peak_src,
-                "kernel": "burgers3d_stage" if "burgers" in w["target"] else "heat3d_stage",
+                "kernel": ("burgers2d_stage_tile" if "burgers" in w["target"] else "heat2d_stage_rows") if two_d else
+                          ("burgers3d_stage" if "burgers" in w["target"] else "heat3d_stage"),
                 "algorithmic_bytes_per_launch": per_launch_bytes,
                 "note": "FP64 WENO5 is bound by the FP64 pipe, not HBM (SURVEY F11); see DESIGN.md" if "burgers" in w["target"] and esz == 8 else ""}
 
@@ -330,7 +353,7 @@ def main():
 
     halo = None
     if nranks > 1:
-        per_nbr = 3 * nx * ny * esz
+        per_nbr = 3 * nx * (1 if two_d else ny) * esz
         nb = 2 if 0 < rank < nranks - 1 else 1
         halo = {"bytes_per_gpu_per_stage": per_nbr * (2 if nranks > 2 else 1), "bytes_per_neighbour": per_nbr,
                 "stages_per_s": 3 * args.steps / (ms * 1e-3),
@@ -343,7 +366,7 @@ def main():
 
     s.close()
     if rank == 0:
-        line = {"metric": "Mcell-updates/s (3D %s, SSP-RK3, %s)" % ("WENO5 Burgers" if "burgers" in w["target"] else "heat", args.precision),
+        line = {"metric": "Mcell-updates/s (%s %s, SSP-RK3, %s)" % ("2D" if two_d or w["target"] == "heat2d_sgpu" else "3D", "WENO5 Burgers" if "burgers" in w["target"] else "heat", args.precision),
                 "value": value, "unit": "Mcell-updates/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic", "config": config,

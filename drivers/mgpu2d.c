@@ -1,0 +1,162 @@
+/* Burgers2d.run / Diffusion2d.run (multi-GPU) -- drop-ins for MultiGPU/Burgers2d_Baseline/main.c and
+ * MultiGPU/Diffusion2d_Baseline/main.c: same argv, stdout block, initial.bin and result.bin (float32,
+ * y-padded to Ny+6 rows, pad rows holding the initial values).
+ *   ADV_NGPUS=P ./Burgers2d.run  tEnd CFL L W Nx Ny block_x block_y        (-DBURGERS)
+ *   ADV_NGPUS=P ./Diffusion2d.run K L W Nx Ny max_iters block_x block_y
+ * `mpirun -np P` becomes ADV_NGPUS=P: ranks are GPUs of this node (y-slabs), one host thread per GPU.
+ * Ny must be divisible by P (the reference silently drops rows). */
+#include <pthread.h>
+#include "common.h"
+
+#define RADIUS ADV_RADIUS
+typedef struct rank_ctx {
+    adv_desc d;
+    adv_solver* solver;
+    struct rank_ctx* all;
+    double tEnd;
+    int iters;
+    double* h_u;            /* global padded array (shared) */
+    unsigned _Ny;
+    double dt, it, t, HtD, DtH, compute;
+    pthread_barrier_t* bar;
+} rank_ctx;
+
+static void* rank_main(void* p)
+{
+    rank_ctx* c = (rank_ctx*)p;
+    const size_t row = (size_t)c->d.nx;
+    adv_solver* s = NULL;
+    if (adv_create(&c->d, &s)) { printf("rank %d: %s\n", c->d.rank, adv_last_error()); exit(-1); }
+    printf("Process %d -> GPU%d\n", c->d.rank, c->d.device);
+    c->solver = s;
+    pthread_barrier_wait(c->bar);
+    if (c->d.nranks > 1 && !(getenv("ADV_HALO") && !strcmp(getenv("ADV_HALO"), "nccl"))) {
+        adv_solver* left = c->d.rank > 0 ? c->all[c->d.rank - 1].solver : NULL;
+        adv_solver* right = c->d.rank < c->d.nranks - 1 ? c->all[c->d.rank + 1].solver : NULL;
+        if (adv_peer_connect_local(s, left, right)) printf("rank %d: peer halo unavailable (%s), using NCCL\n", c->d.rank, adv_last_error());
+    }
+    pthread_barrier_wait(c->bar);
+    const size_t n = adv_local_elems(s);
+    double* h_s_u = (double*)malloc(sizeof(double) * n);
+
+    die_on(adv_init_reference_ic(s), "adv_init_reference_ic");   /* Init_domain(3) + Init_subdomain + H2D */
+    die_on(adv_download(s, h_s_u), "adv_download");
+    memcpy(c->h_u + row * (size_t)c->d.rank * c->_Ny, h_s_u, sizeof(double) * n);
+    pthread_barrier_wait(c->bar);
+    if (c->d.rank == 0) {
+        save_binary_f32(c->h_u, row * (c->d.ny + 2 * RADIUS), "initial.bin");
+        printf("IC saved in Host rank %d\n", 0);
+    }
+    double t0 = now_s();
+    die_on(adv_upload(s, h_s_u), "adv_upload");
+    die_on(adv_sync(s), "adv_sync");
+    c->HtD = now_s() - t0;
+
+    pthread_barrier_wait(c->bar);
+    t0 = now_s();
+#ifdef BURGERS
+    die_on(adv_run_until(s, c->tEnd, -1, &c->dt, &c->it, &c->t), "adv_run_until");
+#else
+    die_on(adv_run_until(s, adv_dt(s) * c->iters, -1, &c->dt, &c->it, &c->t), "adv_run_until");
+#endif
+    die_on(adv_sync(s), "adv_sync");
+    pthread_barrier_wait(c->bar);
+    c->compute = now_s() - t0;
+
+    t0 = now_s();
+    die_on(adv_download(s, h_s_u), "adv_download");
+    c->DtH = now_s() - t0;
+    pthread_barrier_wait(c->bar);
+    /* Merge_domains (Tools.c:165-181): owned rows only */
+    memcpy(c->h_u + row * ((size_t)c->d.rank * c->_Ny + RADIUS), h_s_u + row * RADIUS, sizeof(double) * row * c->_Ny);
+    adv_destroy(s);
+    free(h_s_u);
+    return NULL;
+}
+
+int main(int argc, char** argv)
+{
+    double a1, a2 = 0, L, W;
+    unsigned Nx, Ny, iters = 0;
+    (void)iters; (void)a2;
+    if (argc == 9) {
+#ifdef BURGERS
+        a1 = atof(argv[1]); a2 = atof(argv[2]); L = atof(argv[3]); W = atof(argv[4]);
+        Nx = atoi(argv[5]); Ny = atoi(argv[6]);
+#else
+        a1 = atof(argv[1]); L = atof(argv[2]); W = atof(argv[3]);
+        Nx = atoi(argv[4]); Ny = atoi(argv[5]); iters = atoi(argv[6]);
+#endif
+    } else {
+#ifdef BURGERS
+        printf("Usage: %s tEnd CFL L W Nx Ny block_x block_y\n", argv[0]);
+#else
+        printf("Usage: %s tEnd K L W Nx Ny block_x block_y\n", argv[0]);     /* sic, main.c:49 */
+#endif
+        exit(1);
+    }
+    int P = getenv("ADV_NGPUS") ? atoi(getenv("ADV_NGPUS")) : 1, ndev = 0;
+    die_on(adv_device_count(&ndev), "adv_device_count");
+    if (P < 1 || P > ndev) { printf("ADV_NGPUS=%d but %d B200 device(s) visible\n", P, ndev); exit(-1); }
+
+    const double dx = L / (Nx - 1), dy = W / (Ny - 1);
+    const unsigned NY = Ny + 2 * RADIUS;
+    unsigned char id[128];
+    memset(id, 0, sizeof(id));
+    if (P > 1) die_on(adv_comm_unique_id(id), "adv_comm_unique_id");
+    double* h_u = (double*)malloc(sizeof(double) * Nx * NY);
+    pthread_barrier_t bar;
+    pthread_barrier_init(&bar, NULL, P);
+    rank_ctx* ctx = (rank_ctx*)calloc(P, sizeof(rank_ctx));
+    pthread_t* th = (pthread_t*)calloc(P, sizeof(pthread_t));
+    for (int r = 0; r < P; r++) {
+        adv_desc* d = &ctx[r].d;
+        memset(d, 0, sizeof(*d));
+#ifdef BURGERS
+        d->target = ADV_TARGET_BURGERS2D_MGPU; d->coef = a2; ctx[r].tEnd = a1;
+#else
+        d->target = ADV_TARGET_HEAT2D_MGPU; d->coef = a1; ctx[r].iters = iters;
+#endif
+        d->precision = ADV_F64; d->nx = Nx; d->ny = Ny; d->nz = 1; d->lx = L; d->ly = W;
+        d->device = r; d->nranks = P; d->rank = r;
+        memcpy(d->comm_id, id, 128);
+        ctx[r].h_u = h_u; ctx[r]._Ny = Ny / P; ctx[r].bar = &bar; ctx[r].all = ctx;
+    }
+#ifdef BURGERS
+    printf("dx: %g, dy: %g, final time: %g\n\n", dx, dy, a1);
+#else
+    {
+        const double dt = 1 / (2 * a1 * (1 / dx / dx + 1 / dy / dy)) * 0.8;
+        printf("dx: %g, dy: %g, final time: %g\n\n", dx, dy, dt * iters);
+    }
+#endif
+    for (int r = 0; r < P; r++) pthread_create(&th[r], NULL, rank_main, &ctx[r]);
+    for (int r = 0; r < P; r++) pthread_join(th[r], NULL);
+
+#ifdef BURGERS
+    printf("dt: %g, iterations: %g, final time: %g\n\n", ctx[0].dt, ctx[0].it, ctx[0].t);
+#else
+    printf("dt: %g, iterations: %d, final time: %g\n\n", ctx[0].dt, (int)ctx[0].it, ctx[0].t);
+#endif
+    save_binary_f32(h_u, (size_t)Nx * NY, "result.bin");
+    /* CalcGflops / PrintSummary of the 2-D programs (Tools.c:186-213) */
+    const float gflops = (3 * (unsigned)ctx[0].it) * (double)((Nx * NY) * 1e-9 * FLOPS) / (float)ctx[0].compute;
+#ifdef BURGERS
+    printf("===========================%s=======================\n", "Burgers-2D MPI-GPU-WENO5");
+#else
+    printf("===========================%s=======================\n", "Diffusion-2D MPI-GPU-FD4");
+#endif
+    printf("Optimization                                 :  %s\n", "Pitched Memory");
+    printf("Kernel time ex. data transfers               :  %lf seconds\n", ctx[0].compute);
+    printf("Data transfer(s) HtD                         :  %lf seconds\n", ctx[0].HtD);
+    printf("Data transfer(s) DtH                         :  %lf seconds\n", ctx[0].DtH);
+    printf("===================================================================\n");
+    printf("Total effective GFLOPs                       :  %lf\n", gflops);
+    printf("===================================================================\n");
+    printf("3D Grid Size                                 :  %d x %d\n", Nx, NY);
+    printf("Iterations                                   :  %d x 3 RK steps\n", (int)ctx[0].it);
+    printf("===================================================================\n");
+    print_b200_lines(ctx[0].compute, ctx[0].it, (double)Nx * Ny, 8);
+    free(h_u); free(ctx); free(th);
+    return 0;
+}

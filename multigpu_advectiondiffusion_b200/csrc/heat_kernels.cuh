@@ -125,6 +125,7 @@ heat2d_stage_rows(HeatArgs<REAL> a, int chunk, const REAL* __restrict__ u, const
     const V2 zero = {REAL(0), REAL(0)};
     auto ld = [&](int j) -> V2 { return (j >= 0 && j < a.ny) ? *reinterpret_cast<const V2*>(u + (long long)i + a.pitch * j) : zero; };
     V2 m2 = ld(j0 - 2), m1 = ld(j0 - 1), c = ld(j0), p1 = ld(j0 + 1), p2;
+#pragma unroll 4
     for (int j = j0; j < j1; j++) {
         p2 = ld(j + 2);
         const long long o = (long long)i + a.pitch * j;

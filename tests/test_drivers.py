@@ -25,6 +25,8 @@ def _build():
     ("diffusion2d.run", "PO CFL L W NX NY n_iter block_x block_y"),
     ("Burgers3d_mgpu.run", "tEnd CFL L W H Nx Ny NZ block_x block_y block_z"),
     ("Diffusion3d_mgpu.run", "K L W H Nx Ny NZ max_iters block_x block_y block_z"),
+    ("Burgers2d_mgpu.run", "tEnd CFL L W Nx Ny block_x block_y"),
+    ("Diffusion2d_mgpu.run", "tEnd K L W Nx Ny block_x block_y"),
 ])
 def test_wrong_argc_prints_usage_and_exits_1(exe, usage):
     """Reference behaviour: printf("Usage: ...") then exit(1) (e.g. MultiGPU/Burgers3d_Baseline/main.c:50-54)."""
@@ -86,3 +88,33 @@ def test_heat_and_sgpu_drivers(tmp_path):
     want, info = orc.burgers3d_sgpu(orc.ic_burgers3d_sgpu(32, 32, 32), 0.04)
     res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
     assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6 and "iterations: %g" % info["it"] in r.stdout
+
+
+@pytest.mark.gpu
+def test_2d_mgpu_driver_files(tmp_path):
+    """Burgers2d.run / Diffusion2d.run drop-ins (MultiGPU/*2d_Baseline/main.c): files padded to Ny+6 rows."""
+    _build()
+    nx, ny = 80, 64
+    r = subprocess.run([os.path.join(DRV, "Burgers2d_mgpu.run")] + ["0.1", "0.4", "2.0", "2.0", str(nx), str(ny), "32", "32"],
+                       capture_output=True, text=True, cwd=tmp_path, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "===========================Burgers-2D MPI-GPU-WENO5=======================" in r.stdout
+    assert "3D Grid Size                                 :  %d x %d" % (nx, ny + 6) in r.stdout
+    g = orc.ic_burgers2d_mgpu(nx, ny)
+    want, info = orc.burgers2d_mgpu(g, 0.1)
+    assert "iterations: %g" % info["it"] in r.stdout
+    ini = np.fromfile(tmp_path / "initial.bin", dtype=np.float32)
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert ini.size == res.size == nx * (ny + 6)
+    assert np.array_equal(ini, g.astype(np.float32).ravel())
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    assert np.array_equal(res.reshape(ny + 6, nx)[:3], g[:3].astype(np.float32))
+    r = subprocess.run([os.path.join(DRV, "Diffusion2d_mgpu.run")] + ["1.0", "2.0", "2.0", str(nx), str(ny), "30", "32", "32"],
+                       capture_output=True, text=True, cwd=tmp_path, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    h = orc.ic_heat2d_mgpu(nx, ny)
+    want, info = orc.heat2d_mgpu(h, 30)
+    assert "iterations: %d" % info["it"] in r.stdout
+    res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+    assert np.array_equal(np.fromfile(tmp_path / "initial.bin", dtype=np.float32), h.astype(np.float32).ravel())
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
