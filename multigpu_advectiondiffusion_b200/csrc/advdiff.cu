@@ -289,9 +289,9 @@ static int burgers2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     constexpr int TX = 64, TY = 16, NT = 256;
     dim3 grid((a->nx + TX - 1) / TX, (a->k_end - a->k_begin + TY - 1) / TY, 1), block(NT, 1, 1);
     const REAL* uo_ = a->stage == 1 ? u_in : uo;
-    const size_t shm = sizeof(Burgers2dSmem<REAL, TX, TY>);
+    const size_t shm = sizeof(Burgers2dSmem<REAL>);
 #define LAUNCH_B2D(STAGE_, PEER_) do { \
-        auto kfn = burgers2d_stage_tile<REAL, WENO_JS, TX, TY, NT, STAGE_, PEER_>; \
+        auto kfn = burgers2d_stage_tile<REAL, WENO_JS, STAGE_, PEER_>; \
         CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
         kfn<<<grid, block, shm, st>>>(b, u_in, uo_, u_out); } while (0)
 #define LAUNCH_B2D_S(PEER_) do { \
