@@ -243,9 +243,9 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     // single-GPU case (512^2 lives in L2 and is launch-bound) and for unaligned caller buffers
     if (vec_ok && (slab || (size_t)a->nx * a->ny > ((size_t)1 << 21))) {
         const int rows = h.ke - h.kb, gx = (a->nx / 2 + 1 + 127) / 128;
-        static const int ctas_per_sm = getenv("ADV_HEAT2D_CTAS") ? atoi(getenv("ADV_HEAT2D_CTAS")) : 64;   // A/B switch (measured: 4->128, 8..32->211, 64->226 Gcell-updates/s at 8192^2)
+        static const int ctas_per_sm = getenv("ADV_HEAT2D_CTAS") ? atoi(getenv("ADV_HEAT2D_CTAS")) : 128;  // A/B switch; measured at 8192^2: 16 -> 184, 64 -> 239, 128 -> 253 Gcell-updates/s (equal-length CTAs: many waves keep the tail short)
         int nch = (ctas_per_sm * 148 + gx - 1) / gx;        // many short chunks: loads in flight matter more than the 4 run-in rows ...
-        if (nch > rows / 32) nch = rows / 32;               // ... but chunks of >= 32 rows (4 rows of run-in each)
+        if (nch > rows / 16) nch = rows / 16;               // ... but chunks of >= 16 rows (the 4 run-in rows are L2 hits: neighbouring chunks run together)
         if (nch < 1) nch = 1;
         const int chunk = (rows + nch - 1) / nch;
         dim3 grid(gx, (rows + chunk - 1) / chunk, 1), block(128, 1, 1);

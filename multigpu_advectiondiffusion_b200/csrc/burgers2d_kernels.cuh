@@ -30,7 +30,7 @@ struct Burgers2dSmem {
 };
 
 template <typename REAL, int W, int STAGE, bool PEER>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 burgers2d_stage_tile(BurgersArgs<REAL> a, const REAL* __restrict__ u, const REAL* __restrict__ uo, REAL* __restrict__ out)
 {
     typedef typename V2T<REAL>::type V2;

@@ -104,6 +104,7 @@ __device__ __forceinline__ REAL rk_combine_fast(REAL q, REAL qo, REAL Lq, REAL d
 // cells (one 16-byte access per row), marching a chunk of rows with a 5-deep register queue in y; the x
 // neighbours are the two adjacent aligned pairs, which the neighbouring lanes loaded two rows earlier (L1).
 // Rows [a.kb, a.ke) of `out` are produced; with PEER every produced row is also stored to out2 + off2.
+template <bool B> struct BoolTag2 { static constexpr bool value = B; };
 template <typename REAL> struct Pair2T;
 template <> struct Pair2T<double> { typedef double2 type; };
 template <> struct Pair2T<float> { typedef float2 type; };
@@ -123,31 +124,35 @@ heat2d_stage_rows(HeatArgs<REAL> a, int chunk, const REAL* __restrict__ u, const
     const bool rkx0 = i >= a.rk.lo[0] && i <= a.rk.hi[0], rkx1 = has1 && i + 1 >= a.rk.lo[0] && i + 1 <= a.rk.hi[0];
     const bool ldl = i >= 2, ldr = (long long)i + 3 < a.pitch;
     const V2 zero = {REAL(0), REAL(0)};
-    auto ld = [&](int j) -> V2 { return (j >= 0 && j < a.ny) ? *reinterpret_cast<const V2*>(u + (long long)i + a.pitch * j) : zero; };
+    const REAL* __restrict__ up = u + i;
+    auto ld = [&](int j) -> V2 { return (j >= 0 && j < a.ny) ? *reinterpret_cast<const V2*>(up + a.pitch * j) : zero; };
     V2 m2 = ld(j0 - 2), m1 = ld(j0 - 1), c = ld(j0), p1 = ld(j0 + 1), p2;
-#pragma unroll 4
-    for (int j = j0; j < j1; j++) {
-        p2 = ld(j + 2);
+
+    // one row; FAST: both cells inside the Laplacian and RK boxes, row j+2 exists -- no tests, so that the
+    // unrolled steady-state loop below can issue the loads of several rows back to back
+    auto row = [&](int j, auto fast_tag) {
+        constexpr bool FAST = decltype(fast_tag)::value;
         const long long o = (long long)i + a.pitch * j;
-        const bool rky = j >= a.rk.lo[1] && j <= a.rk.hi[1];
-        const bool lapy = j >= a.lap.lo[1] && j <= a.lap.hi[1];
+        p2 = FAST ? *reinterpret_cast<const V2*>(u + o + 2 * a.pitch) : ld(j + 2);
+        const bool rky = FAST || (j >= a.rk.lo[1] && j <= a.rk.hi[1]);
+        const bool lapy = FAST || (j >= a.lap.lo[1] && j <= a.lap.hi[1]);
         V2 res = c;
-        if (rky && (rkx0 || rkx1)) {
+        if (FAST || (rky && (rkx0 || rkx1))) {
             V2 Lu = zero;
-            if (lapy && (lapx0 || lapx1)) {
-                const V2 L = ldl ? *reinterpret_cast<const V2*>(u + o - 2) : zero;
-                const V2 R = ldr ? *reinterpret_cast<const V2*>(u + o + 2) : zero;
-                if (lapx0) Lu.x = a.kx * (-L.x + REAL(16) * L.y - REAL(30) * c.x + REAL(16) * c.y - R.x) +
-                                  a.ky * (-m2.x + REAL(16) * m1.x - REAL(30) * c.x + REAL(16) * p1.x - p2.x);
-                if (lapx1) Lu.y = a.kx * (-L.y + REAL(16) * c.x - REAL(30) * c.y + REAL(16) * R.x - R.y) +
-                                  a.ky * (-m2.y + REAL(16) * m1.y - REAL(30) * c.y + REAL(16) * p1.y - p2.y);
+            if (FAST || (lapy && (lapx0 || lapx1))) {
+                const V2 L = (FAST || ldl) ? *reinterpret_cast<const V2*>(u + o - 2) : zero;
+                const V2 R = (FAST || ldr) ? *reinterpret_cast<const V2*>(u + o + 2) : zero;
+                if (FAST || lapx0) Lu.x = a.kx * (-L.x + REAL(16) * L.y - REAL(30) * c.x + REAL(16) * c.y - R.x) +
+                                          a.ky * (-m2.x + REAL(16) * m1.x - REAL(30) * c.x + REAL(16) * p1.x - p2.x);
+                if (FAST || lapx1) Lu.y = a.kx * (-L.y + REAL(16) * c.x - REAL(30) * c.y + REAL(16) * R.x - R.y) +
+                                          a.ky * (-m2.y + REAL(16) * m1.y - REAL(30) * c.y + REAL(16) * p1.y - p2.y);
             }
             V2 qo = c;
             if (STAGE != 1) qo = *reinterpret_cast<const V2*>(uo + o);
-            if (rkx0) res.x = rk_combine_fast<REAL, STAGE>(c.x, qo.x, Lu.x, a.dt);
-            if (rkx1) res.y = rk_combine_fast<REAL, STAGE>(c.y, qo.y, Lu.y, a.dt);
+            if (FAST || rkx0) res.x = rk_combine_fast<REAL, STAGE>(c.x, qo.x, Lu.x, a.dt);
+            if (FAST || rkx1) res.y = rk_combine_fast<REAL, STAGE>(c.y, qo.y, Lu.y, a.dt);
         }
-        if (has1) {
+        if (FAST || has1) {
             *reinterpret_cast<V2*>(out + o) = res;
             if (PEER) *reinterpret_cast<V2*>(a.out2 + a.off2 + o) = res;
         } else {
@@ -155,7 +160,15 @@ heat2d_stage_rows(HeatArgs<REAL> a, int chunk, const REAL* __restrict__ u, const
             if (PEER) a.out2[a.off2 + o] = res.x;
         }
         m2 = m1; m1 = c; c = p1; p1 = p2;
-    }
+    };
+    const bool fast_x = lapx0 && lapx1 && rkx0 && rkx1 && ldl && ldr;
+    const int f0 = fast_x ? max(j0, max(a.lap.lo[1], a.rk.lo[1])) : j1;
+    const int f1 = fast_x ? min(j1, min(min(a.lap.hi[1], a.rk.hi[1]) + 1, a.ny - 2)) : j1;      // fast rows [f0, f1)
+    int j = j0;
+    for (; j < min(f0, j1); j++) row(j, BoolTag2<false>());
+#pragma unroll 4
+    for (; j < f1; j++) row(j, BoolTag2<true>());
+    for (; j < j1; j++) row(j, BoolTag2<false>());
 }
 
 template <typename REAL> struct Vec2T;
