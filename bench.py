@@ -70,51 +70,77 @@ def ncu_profile(workload):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons every 50 ms while the timed region runs (B200_PROFILING.md)."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock, power and throttle reasons every 50 ms while the timed region runs (the quantities of the
+    nvidia-smi clocks line in B200_PROFILING.md, read through NVML in a thread of this process).  NVML is
+    initialised in __init__, i.e. BEFORE the warm-up: starting an `nvidia-smi -lms` process right before
+    the timed region put its multi-second start-up on a multi-GPU box inside the region and stalled the
+    GPUs it enumerates (4 GPUs, heat 512^3: 1.53 ms/step without a sampler, 16.6 ms/step with one)."""
 
     def __init__(self, index):
         self.index = index
-        self.proc = None
+        self.rows, self.h, self.nv, self.thread = [], None, None, None
+        self.stop_flag = False
+        if index is None:
+            return
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # torch/CUDA ordinals follow CUDA_VISIBLE_DEVICES; NVML's do not
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                tok = vis.split(",")[index].strip()
+                phys = int(tok) if tok.isdigit() else None
+                if phys is None:
+                    self.h = pynvml.nvmlDeviceGetHandleByUUID(tok)
+            if self.h is None:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.sample()               # first query pays NVML's lazy set-up
+            self.rows = []
+        except Exception:
+            self.h = None
+
+    def sample(self):
+        nv = self.nv
+        try:
+            reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM), nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM),
+                          nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0, int(reasons)))
+
+    def _loop(self):
+        while not self.stop_flag:
+            try:
+                self.sample()
+            except Exception:
+                break
+            time.sleep(0.05)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "50"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            time.sleep(0.15)            # let the first sample land before the timed region starts
-        except Exception:
-            self.proc = None
+        if self.h is None:
+            return
+        import threading
+        self.stop_flag = False
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
 
     def summary(self):
-        rows = []
-        if self.proc is not None:
-            time.sleep(0.06)
-            self.proc.terminate()
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
             try:
-                out, _ = self.proc.communicate(timeout=5)
+                self.sample()           # one more at the end of the region
             except Exception:
-                self.proc.kill()
-                out = ""
-            rows = [[x.strip() for x in ln.split(",")] for ln in out.splitlines() if ln.strip()]
-
-        def num(x):
-            try:
-                return float(x)
-            except ValueError:
-                return None
-        sm = [num(r[0]) for r in rows if num(r[0]) is not None]
-        mx = [num(r[1]) for r in rows if len(r) > 1 and num(r[1]) is not None]
-        pw = [num(r[2]) for r in rows if len(r) > 2 and num(r[2]) is not None]
-        reasons = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in rows:
-            for n, v in zip(names, r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "reasons": sorted(reasons), "samples": len(rows)}
+                pass
+        rows = self.rows
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        reasons = sorted(n for n, b in bits.items() if any(r[3] & b for r in rows))
+        return {"sm_mhz": float(np.median([r[0] for r in rows])) if rows else None,
+                "sm_max_mhz": float(max(r[1] for r in rows)) if rows else None,
+                "power_w_max": float(max(r[2] for r in rows)) if rows else None,
+                "reasons": reasons, "samples": len(rows), "source": "NVML (nvidia_ml_py), rank 0's GPU, 50 ms period"}
 
 
 def cpu_sample(w, precision_bytes, target_seconds=12.0):
@@ -283,9 +309,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    # one sampler for the job (rank 0's GPU), NVML initialised before the warm-up
+    sampler = ClockSampler(dev if rank == 0 and not os.environ.get("ADV_NO_SAMPLER") else None)
     s.step(args.warmup)
     s.sync()
-    sampler = ClockSampler(dev)
     barrier()
     sampler.start()
     l0 = s.kernel_launches
