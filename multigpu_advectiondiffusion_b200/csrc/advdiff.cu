@@ -10,6 +10,7 @@
 
 #include <new>
 #include <stdint.h>
+#include <thread>
 #include <vector>
 
 #include "burgers_kernels.cuh"
@@ -650,7 +651,16 @@ static void reference_ic_local(const adv_solver* s, REAL* h)
     const REAL dx = (REAL)s->dx, dy = (REAL)s->dy, dz = (REAL)s->dz;
     const int NZ = is_mgpu(d.target) ? s->nsplit + 2 * ADV_RADIUS : d.nz; // global stored planes (rows)
     const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;            // Init_subdomain, Tools.c:181-200
-    for (int kl = 0; kl < s->nzs; kl++) {
+    // every value depends on its own indices only: slab units are spread over host threads (same libm calls,
+    // same bits; at 512^3 the serial loop was the longest part of a driver's set-up)
+    const int units = s->nzs;
+    int nthr = (int)std::thread::hardware_concurrency();
+    if (nthr < 1) nthr = 1;
+    if (nthr > 16) nthr = 16;
+    if ((size_t)nx * ny * units < ((size_t)1 << 20)) nthr = 1;
+    if (nthr > units) nthr = units;
+    auto fill = [&](int kl0, int kl1) {
+    for (int kl = kl0; kl < kl1; kl++) {
         const int k = kl + kg0;
         for (int j = 0; j < ny; j++)
             for (int i = 0; i < nx; i++) {
@@ -694,6 +704,12 @@ static void reference_ic_local(const adv_solver* s, REAL* h)
                 h[o] = v;
             }
     }
+    };
+    if (nthr == 1) { fill(0, units); return; }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthr; t++)
+        pool.emplace_back(fill, (int)((long long)units * t / nthr), (int)((long long)units * (t + 1) / nthr));
+    for (auto& th : pool) th.join();
 }
 
 extern "C" int adv_init_reference_ic(adv_solver* s)
