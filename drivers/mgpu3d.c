@@ -40,6 +40,9 @@ static void* rank_main(void* p)
         if (adv_peer_connect_local(s, left, right)) printf("rank %d: peer halo unavailable (%s), using NCCL\n", c->d.rank, adv_last_error());
     }
     pthread_barrier_wait(c->bar);
+    /* every rank must have ended up on the same exchange path: a mix would wait forever */
+    for (int r = 0; r < c->d.nranks; r++)
+        if (adv_halo_mode(c->all[r].solver) != adv_halo_mode(s)) { printf("ranks disagree on the halo exchange path\n"); exit(-1); }
     const size_t n = adv_local_elems(s);
     double* h_s_u = (double*)malloc(sizeof(double) * n);
 

@@ -132,17 +132,19 @@ static int heat_args_from(const adv_stage_args* a, HeatArgs<REAL>& h)
 typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn lookup_tmap_encode()
+{
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+        return (tmap_encode_fn)p;
+    return nullptr;
+}
 static tmap_encode_fn get_tmap_encode()
 {
-    static tmap_encode_fn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (tmap_encode_fn)p;
-    }
+    // function-local static: initialised exactly once even when the ranks are threads of one process (a
+    // hand-rolled "tried" flag let a second thread see "not available" and pick a different halo path)
+    static const tmap_encode_fn fn = lookup_tmap_encode();
     return fn;
 }
 
@@ -791,18 +793,18 @@ __global__ void halo_wait_kernel(const volatile unsigned* flag, unsigned value)
 }
 
 typedef CUresult (*stream_wait32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static stream_wait32_fn lookup_stream_wait32()
+{
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (!getenv("ADV_HALO_SPIN_WAIT") &&
+        cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+        return (stream_wait32_fn)p;
+    return nullptr;
+}
 static stream_wait32_fn get_stream_wait32()
 {
-    static stream_wait32_fn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (!getenv("ADV_HALO_SPIN_WAIT") &&
-            cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (stream_wait32_fn)p;
-    }
+    static const stream_wait32_fn fn = lookup_stream_wait32();     // thread-safe one-time lookup
     return fn;
 }
 

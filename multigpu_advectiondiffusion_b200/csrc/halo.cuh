@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <mutex>
 #include <stdio.h>
 #include <string.h>
 
@@ -39,6 +40,8 @@ struct NcclApi {
     {
         static NcclApi api;
         static int state = 0;   // 0 untried, 1 ok, -1 failed
+        static std::mutex mu;   // ranks may be threads of one process (drivers/mgpu*.c)
+        std::lock_guard<std::mutex> lock(mu);
         if (state == 1) return &api;
         if (state == -1) { snprintf(err, errlen, "NCCL is not loadable (libnccl.so.2)"); return nullptr; }
         void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);

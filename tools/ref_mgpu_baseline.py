@@ -34,27 +34,52 @@ def run(exe, args, cwd, env):
 
 
 def case(name, ref_exe, our_exe, args, cells, P, out):
+    only = os.environ.get("REFMGPU_ONLY")                   # e.g. REFMGPU_ONLY=Burgers3d,Diffusion3d
+    if only and not any(name.startswith(x) for x in only.split(",")):
+        return
     try:
         _case(name, ref_exe, our_exe, args, cells, P, out)
     except Exception as e:              # keep what finished: a hung program must not cost the whole run
-        out[name] = {"argv": " ".join(str(a) for a in args), "ranks": P, "error": str(e)[-400:]}
-    print(json.dumps({name: out[name]}), file=sys.stderr, flush=True)
+        out.setdefault(name, {})["error"] = str(e)[-400:]
+    print(json.dumps({name: out.get(name)}), file=sys.stderr, flush=True)
 
 
 def _case(name, ref_exe, our_exe, args, cells, P, out):
+    res = {"argv": " ".join(str(a) for a in args), "ranks": P}
+    out[name] = res
     with tempfile.TemporaryDirectory() as d_ref, tempfile.TemporaryDirectory() as d_our:
-        tr, itr = run(os.path.join(REF, ref_exe), args, d_ref, dict(os.environ, ADV_MPI_NP=str(P)))
-        to, ito = run(os.path.join(DRV, our_exe), args, d_our, dict(os.environ, ADV_NGPUS=str(P)))
-        r = np.fromfile(os.path.join(d_ref, "result.bin"), dtype=np.float32)
-        o = np.fromfile(os.path.join(d_our, "result.bin"), dtype=np.float32)
-        i0 = np.fromfile(os.path.join(d_ref, "initial.bin"), dtype=np.float32)
-        i1 = np.fromfile(os.path.join(d_our, "initial.bin"), dtype=np.float32)
-    out[name] = {"argv": " ".join(str(a) for a in args), "ranks": P, "iterations": [itr, ito],
-                 "reference_sm100": {"seconds": tr, "Mcell_updates_per_s": cells * 3 * itr / tr / 1e6},
-                 "this_repo": {"seconds": to, "Mcell_updates_per_s": cells * 3 * ito / to / 1e6},
-                 "speedup": tr / to * (ito / itr),
-                 "result_bin_elems": int(r.size), "result_bin_max_abs_diff": float(np.abs(r - o).max()),
-                 "result_bin_max_abs": float(np.abs(r).max()), "initial_bin_identical": bool(np.array_equal(i0, i1))}
+        files = {}
+        for key, exe, cwd, env in (("this_repo", os.path.join(DRV, our_exe), d_our, dict(os.environ, ADV_NGPUS=str(P))),
+                                   ("reference_sm100", os.path.join(REF, ref_exe), d_ref, dict(os.environ, ADV_MPI_NP=str(P)))):
+            print("[%s] %s ..." % (name, key), file=sys.stderr, flush=True)
+            try:
+                t, it = run(exe, args, cwd, env)
+                res[key] = {"seconds": t, "iterations": it, "Mcell_updates_per_s": cells * 3 * it / t / 1e6}
+                files[key] = (np.fromfile(os.path.join(cwd, "result.bin"), dtype=np.float32),
+                              np.fromfile(os.path.join(cwd, "initial.bin"), dtype=np.float32))
+            except Exception as e:
+                res[key] = {"error": str(e)[-400:]}
+        if len(files) == 2:
+            (r, i0), (o, i1) = files["reference_sm100"], files["this_repo"]
+            res["speedup"] = res["this_repo"]["Mcell_updates_per_s"] / res["reference_sm100"]["Mcell_updates_per_s"]
+            res["result_bin_elems"] = int(r.size)
+            res["result_bin_max_abs_diff"] = float(np.abs(r - o).max())
+            res["result_bin_max_abs"] = float(np.abs(r).max())
+            res["initial_bin_identical"] = bool(np.array_equal(i0, i1))
+        # three-way check against the CPU oracle (= the reference's program-order semantics, pinned bit-exactly to
+        # its kernels): tells which side a disagreement comes from
+        if os.environ.get("REFMGPU_ORACLE") and name in ("Burgers3d_Baseline", "Diffusion3d_Baseline") and files:
+            sys.path.insert(0, ROOT)
+            from oracle import oracle as orc
+            a = [float(x) for x in args]
+            nx, ny, nz = int(args[-6 if name.startswith("Burgers") else -7]), int(args[-5 if name.startswith("Burgers") else -6]), int(args[-4 if name.startswith("Burgers") else -5])
+            if name.startswith("Burgers"):
+                want, _ = orc.burgers3d_mgpu(orc.ic_burgers3d_mgpu(nx, ny, nz, a[2], a[3], a[4]), a[0], a[1], a[2], a[3], a[4])
+            else:
+                want, _ = orc.heat3d(orc.ic_heat3d_mgpu(nx, ny, nz), int(args[7]), "mgpu", a[0], a[1], a[2], a[3])
+            w32 = want.astype(np.float32).ravel()
+            for key, (rb, _) in files.items():
+                res[key]["result_bin_max_abs_diff_vs_cpu_oracle"] = float(np.abs(rb - w32).max())
 
 
 def main():
