@@ -118,3 +118,36 @@ def test_2d_mgpu_driver_files(tmp_path):
     res = np.fromfile(tmp_path / "result.bin", dtype=np.float32)
     assert np.array_equal(np.fromfile(tmp_path / "initial.bin", dtype=np.float32), h.astype(np.float32).ravel())
     assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+
+
+@pytest.mark.gpu
+def test_mgpu_drivers_on_two_gpus_match_the_oracle(tmp_path):
+    """In-process ranks (one host thread per GPU, adv_peer_connect_local): all four multi-GPU drop-ins at
+    ADV_NGPUS=2 against the CPU oracle through result.bin.  Regression test for ranks ending up on
+    different halo paths (one-time lookups raced between the rank threads and the heat driver stalled)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    _build()
+    env = dict(os.environ, ADV_NGPUS="2")
+
+    def run(exe, args):
+        r = subprocess.run([os.path.join(DRV, exe)] + [str(a) for a in args], capture_output=True, text=True, cwd=tmp_path, timeout=60, env=env)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert "Process 1 -> GPU1" in r.stdout
+        return np.fromfile(tmp_path / "result.bin", dtype=np.float32)
+
+    nx, ny, nz = 64, 40, 96         # the slab interface cuts the peak of the initial Gaussian / pulse
+    res = run("Burgers3d_mgpu.run", [0.05, 0.3, 2.0, 2.0, 2.0, nx, ny, nz, 8, 8, 8])
+    want, _ = orc.burgers3d_mgpu(orc.ic_burgers3d_mgpu(nx, ny, nz), 0.05)
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    res = run("Diffusion3d_mgpu.run", [1.0, 2.0, 2.0, 2.0, nx, ny, nz, 12, 64, 4, 1])
+    want, _ = orc.heat3d(orc.ic_heat3d_mgpu(nx, ny, nz), 12, "mgpu", L=2.0, W=2.0, H=2.0)
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    nx, ny = 96, 128
+    res = run("Burgers2d_mgpu.run", [0.1, 0.4, 2.0, 2.0, nx, ny, 32, 32])
+    want, _ = orc.burgers2d_mgpu(orc.ic_burgers2d_mgpu(nx, ny), 0.1)
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+    res = run("Diffusion2d_mgpu.run", [1.0, 2.0, 2.0, nx, ny, 40, 32, 32])
+    want, _ = orc.heat2d_mgpu(orc.ic_heat2d_mgpu(nx, ny), 40)
+    assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
