@@ -242,3 +242,52 @@ def save_binary(u, path):
 def rel_err(a, b):
     """Parity metric of BASELINE.md section 3: max|a-b| / max|b|."""
     return float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64))) / np.max(np.abs(b)))
+
+
+# ---------------------------------------------------------------- Oracle B: C transcription of the Matlab prototypes
+_MLB = None
+
+
+def mlb():
+    """oracle/libmatlab_port.so (matlab_port.c) -- second opinion only, see its header."""
+    global _MLB
+    if _MLB is None:
+        path = os.path.join(_HERE, "libmatlab_port.so")
+        if not os.path.exists(path):
+            build()
+        _MLB = C.CDLL(path, mode=os.RTLD_LOCAL)
+    return _MLB
+
+
+def mlb_heat3d(u0, nsteps, D=1.0, L=10.0, W=10.0, H=10.0, dt=None):
+    u = np.array(u0, dtype=np.float64, copy=True, order="C")
+    nz, ny, nx = u.shape
+    dx, dy, dz = L / (nx - 1), W / (ny - 1), H / (nz - 1)
+    if dt is None:
+        dt = 1 / (2 * D * (1 / dx**2 + 1 / dy**2 + 1 / dz**2)) * 0.9          # heat3d.m:38
+    f = mlb().mlb_heat3d_run
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_double] * 4 + [C.c_int]
+    assert f(_ptr(u), nx, ny, nz, D / dx**2, D / dy**2, D / dz**2, dt, nsteps) == 0
+    return u, dict(dt=dt)
+
+
+def mlb_heat2d(u0, nsteps, D=1.0, L=10.0, W=10.0, dt=None):
+    u = np.array(u0, dtype=np.float64, copy=True, order="C")
+    ny, nx = u.shape
+    dx, dy = L / (nx - 1), W / (ny - 1)
+    if dt is None:
+        dt = 1 / (2 * D * (1 / dx**2 + 1 / dy**2)) * 0.9                         # heat2d.m:36
+    f = mlb().mlb_heat2d_run
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_double] * 3 + [C.c_int]
+    assert f(_ptr(u), nx, ny, D / dx**2, D / dy**2, dt, nsteps) == 0
+    return u, dict(dt=dt)
+
+
+def mlb_burgers3d(u0, tEnd, CFL=0.3, dx=None, dy=None, dz=None, dynamic_dt=False, max_steps=-1):
+    u = np.array(u0, dtype=np.float64, copy=True, order="C")
+    nz, ny, nx = u.shape
+    f = mlb().mlb_burgers3d_run
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_double] * 5 + [C.c_int, C.c_int] + [C.POINTER(C.c_double)] * 3
+    dt, it, t = C.c_double(), C.c_double(), C.c_double()
+    assert f(_ptr(u), nx, ny, nz, dx, dy, dz, CFL, tEnd, int(dynamic_dt), max_steps, C.byref(dt), C.byref(it), C.byref(t)) == 0
+    return u, dict(dt=dt.value, it=it.value, t=t.value)

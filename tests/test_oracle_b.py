@@ -1,0 +1,56 @@
+"""Oracle A (oracle/advdiff_oracle.c, the CUDA programs restated and pinned to the reference's kernels) against
+Oracle B (oracle/matlab_port.c, an independent C transcription of the reference's Matlab prototypes -- its CPU
+implementation of the same path).  The two differ in operand order and in boundary treatment
+(frozen frames / pad planes vs edge-replicated ghost cells and a zeroed outer layer), so they must agree to
+rounding exactly where neither boundary treatment can have reached yet.  CPU only."""
+import numpy as np
+
+from oracle import oracle as orc
+
+TOL = 1e-13
+
+
+def test_heat3d_a_vs_b_whole_domain():
+    # SingleGPU/Diffusion3d_baselineCode and heat3d.m + Laplace3d.m share frame (2) and boundary values (0)
+    u0 = orc.ic_heat3d_sgpu(40, 36, 32)
+    a, ai = orc.heat3d(u0, 25, "baseline")
+    b, _ = orc.mlb_heat3d(u0, 25, dt=ai["dt"])
+    assert orc.rel_err(b, a) <= TOL
+    # the prototype's own dt formula (heat3d.m:38, 1/dx^2) is the driver's (main.cpp:58, 1/dx/dx) up to an ulp
+    assert abs(orc.mlb_heat3d(u0, 0)[1]["dt"] / ai["dt"] - 1) < 1e-15
+
+
+def test_heat2d_a_vs_b_interior():
+    # SingleGPU/Diffusion2d freezes a frame of 3, Laplace2d.m one of 2: compare inside the domain of dependence
+    steps = 6
+    u0 = orc.ic_heat2d_sgpu(96, 80) + 0.1 * np.random.default_rng(2).random((80, 96))
+    a, ai = orc.heat2d(u0, steps)
+    b, _ = orc.mlb_heat2d(u0, steps, dt=ai["dt"])
+    m = 3 + 2 * 3 * steps                   # stencil radius 2, three stages per step
+    assert np.abs(a - b)[m:-m, m:-m].max() / np.abs(a).max() <= TOL
+    assert np.abs(a - b).max() > 1e-6       # ... and the frames really differ outside it
+
+
+def test_burgers3d_a_vs_b_interior():
+    # MultiGPU/Burgers3d_Baseline (pad planes, i=2/j=2 artefacts) vs LFWENO5FDM3d.m (replicated ghost cells)
+    nx, ny, nz, steps = 56, 52, 50, 2
+    g = orc.ic_burgers3d_mgpu(nx, ny, nz) + 0.2 * np.random.default_rng(3).random((nz + 6, ny, nx))
+    a, ai = orc.burgers3d_mgpu(g, 1e9, max_steps=steps)
+    b, bi = orc.mlb_burgers3d(g, 1e9, CFL=0.3, dx=2.0 / (nx - 1), dy=2.0 / (ny - 1), dz=2.0 / (nz - 1), max_steps=steps)
+    assert ai == bi
+    m = 3 + 3 * 3 * steps                   # stencil radius 3, three stages per step
+    d = np.abs(a - b)
+    assert d[m:-m, m:-m, m:-m].max() / np.abs(a).max() <= TOL
+    assert d.max() > 1e-6
+
+
+def test_matlab_dynamic_time_step():
+    """LFWENO5FDM3d.m:71: dt = CFL*dx/max|u|.  The CUDA drivers fix max|u| = 1 (main.c:193); for the Gaussian
+    pulse (max 1 at t = 0, decaying) the prototype therefore takes the same first step and longer ones after."""
+    n = 40
+    g = orc.ic_burgers3d_sgpu(n, n, n)
+    dx = 2.0 / (n - 1)
+    _, fixed = orc.mlb_burgers3d(g, 0.05, CFL=0.3, dx=dx, dy=dx, dz=dx, dynamic_dt=False)
+    u, dyn = orc.mlb_burgers3d(g, 0.05, CFL=0.3, dx=dx, dy=dx, dz=dx, dynamic_dt=True)
+    assert dyn["t"] == fixed["t"] == 0.05 and dyn["it"] <= fixed["it"]
+    assert np.isfinite(u).all() and u.max() <= 1.0 + 1e-3 and u.min() >= -1e-3      # the pulse has amplitude 1
