@@ -48,11 +48,15 @@ int mlb_heat3d_run(double* u, int nx, int ny, int nz, double Dx, double Dy, doub
     for (int it = 0; it < nsteps; it++) {
         memcpy(uo, u, n*sizeof(double));
         mlb_laplace3d(u, dF, nx, ny, nz, Dx, Dy, Dz);
+        #pragma omp parallel for schedule(static)
         for (size_t o = 0; o < n; o++) u[o] = uo[o]+dt*dF[o];
         mlb_laplace3d(u, dF, nx, ny, nz, Dx, Dy, Dz);
+        #pragma omp parallel for schedule(static)
         for (size_t o = 0; o < n; o++) u[o] = 0.75*uo[o]+0.25*(u[o]+dt*dF[o]);
         mlb_laplace3d(u, dF, nx, ny, nz, Dx, Dy, Dz);
+        #pragma omp parallel for schedule(static)
         for (size_t o = 0; o < n; o++) u[o] = (uo[o]+2*(u[o]+dt*dF[o]))/3;
+        #pragma omp parallel for schedule(static)
         for (int k = 0; k < nz; k++) for (int j = 0; j < ny; j++) for (int i = 0; i < nx; i++)
             if (i==0 || i==nx-1 || j==0 || j==ny-1 || k==0 || k==nz-1) u[IDX(i,j,k)] = 0;
     }
