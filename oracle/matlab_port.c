@@ -3,10 +3,12 @@
  * C transcription of the reference's Matlab prototypes -- its CPU implementation of the same path -- kept
  * independent of advdiff_oracle.c (which restates the CUDA programs): same operators, Matlab's own operand
  * order, boundary treatment (edge-replicated ghost cells, zeroed outer layer for heat) and, optionally,
- * its dynamic time step dt = CFL*dx/max|u|.  No Matlab/Octave exists on this image, so this port is NOT
- * pinned to an executed Matlab run ("parity unpinned" for this file); tests/test_oracle_b.py uses it only as
- * a second opinion: it must agree with Oracle A to rounding wherever the two boundary treatments cannot have
- * reached yet.  Never linked or imported by the product.
+ * its dynamic time step dt = CFL*dx/max|u|.  No Matlab/Octave exists on this image; the heat routines are
+ * pinned instead to the one executed Matlab run the reference recorded: they reproduce every printed digit of
+ * the L1 / Linf tables in Matlab_Prototipes/DiffusionNd/TestingAccuracy.log:49-72 (tests/test_oracle_b.py).
+ * The Burgers routine has no such record ("parity unpinned" for mlb_burgers3d_run).  Use: a second opinion --
+ * it must agree with Oracle A to rounding wherever the two boundary treatments cannot have reached yet.
+ * Never linked or imported by the product.
  *
  *   heat3d.m:48-77 + Laplace3d.m:32-60 ('OMP' strategy)     -> mlb_heat3d_run
  *   heat2d.m:47-75 + Laplace2d.m:6-16                        -> mlb_heat2d_run

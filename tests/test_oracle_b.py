@@ -54,3 +54,53 @@ def test_matlab_dynamic_time_step():
     u, dyn = orc.mlb_burgers3d(g, 0.05, CFL=0.3, dx=dx, dy=dx, dz=dx, dynamic_dt=True)
     assert dyn["t"] == fixed["t"] == 0.05 and dyn["it"] <= fixed["it"]
     assert np.isfinite(u).all() and u.max() <= 1.0 + 1e-3 and u.min() >= -1e-3      # the pulse has amplitude 1
+
+
+# ---------------------------------------------------------------------------------------------------------
+# The reference's only recorded numbers for this path: Matlab_Prototipes/DiffusionNd/TestingAccuracy.log:49-72,
+# the L1 / Linf error tables of TestingAccuracy.m (diffusion2dTest.m / diffusion3dTest.m against the analytic
+# Gaussian).  The log does not say which parameters produced it; tEnd = 1.0, factor = 0.9 and nc = 10, 20, 40, 80
+# reproduce every printed digit, which pins Oracle B (and through the tests above Oracle A's interior
+# arithmetic) to an executed run of the reference's own CPU code.
+# ---------------------------------------------------------------------------------------------------------
+LOG_2D = {10: (2.97e-01, 2.65e-02), 20: (3.42e-02, 2.96e-03), 40: (5.14e-03, 3.59e-04), 80: (2.99e-03, 2.64e-04)}
+LOG_3D = {10: (3.99e-01, 7.31e-03), 20: (2.75e-02, 5.04e-04), 40: (1.35e-02, 3.29e-04), 80: (4.70e-03, 8.33e-05)}
+
+
+def _accuracy_test(n, dim, tFinal=1.0, param=0.9):
+    """diffusion{2,3}dTest.m:11-66 -- including its loop order: dt is clipped AFTER the step that crosses tFinal."""
+    D, t0, L = 1.0, 0.1, 10.0
+    dx = L / (n - 1)
+    xs = -L / 2 + dx * np.arange(n)
+    grids = np.meshgrid(*([xs] * dim), indexing="ij")
+    r2 = sum(g**2 for g in grids)
+    u = np.exp(-r2 / (4 * D * t0))
+    uE = (t0 / tFinal) ** (dim / 2) * np.exp(-r2 / (4 * D * tFinal))
+    dt = 1 / (2 * D * (dim / dx**2)) * param
+    t = t0
+    while t < tFinal:
+        if dim == 3:
+            u, _ = orc.mlb_heat3d(u, 1, D=D, L=L, W=L, H=L, dt=dt)
+        else:
+            u, _ = orc.mlb_heat2d(u, 1, D=D, L=L, W=L, dt=dt)
+        if t + dt > tFinal:
+            dt = tFinal - t
+        t = t + dt
+    err = np.abs(uE - u)
+    return dx**dim * err.sum(), err.max()
+
+
+def _same_3_digits(got, logged):
+    return "%.2e" % got == "%.2e" % logged
+
+
+def test_oracle_b_reproduces_the_reference_accuracy_log_2d():
+    for n, (l1, linf) in LOG_2D.items():
+        g1, ginf = _accuracy_test(n, 2)
+        assert _same_3_digits(g1, l1) and _same_3_digits(ginf, linf), (n, g1, ginf)
+
+
+def test_oracle_b_reproduces_the_reference_accuracy_log_3d():
+    for n, (l1, linf) in LOG_3D.items():
+        g1, ginf = _accuracy_test(n, 3)
+        assert _same_3_digits(g1, l1) and _same_3_digits(ginf, linf), (n, g1, ginf)
