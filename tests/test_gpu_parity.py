@@ -251,3 +251,38 @@ def test_graph_replay_is_bit_identical_to_plain_launches(target, shape, kw):
         assert a.kernel_launches == b.kernel_launches == 48
     assert np.array_equal(ua, ub)
     assert np.isfinite(ua).all() and not np.array_equal(ua, u0)
+
+
+def test_gpu_reproduces_the_reference_accuracy_log_3d():
+    """The reference's only recorded numbers for this path (Matlab_Prototipes/DiffusionNd/TestingAccuracy.log:67-72,
+    heat 3-D L1 / Linf errors against the analytic Gaussian; parameters recovered in tests/test_oracle_b.py):
+    the same loop driven through adv_heat3d_stage_f64 on caller-owned device memory prints the same digits."""
+    import torch
+    log = {20: (2.75e-02, 5.04e-04), 40: (1.35e-02, 3.29e-04)}
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    for n, (l1, linf) in log.items():
+        D, t0, L, tFinal = 1.0, 0.1, 10.0, 1.0
+        dx = L / (n - 1)
+        xs = -L / 2 + dx * np.arange(n)
+        X, Y, Z = np.meshgrid(xs, xs, xs, indexing="ij")
+        r2 = X**2 + Y**2 + Z**2
+        uE = (t0 / tFinal) ** 1.5 * np.exp(-r2 / (4 * D * tFinal))
+        A = torch.from_numpy(np.ascontiguousarray(np.exp(-r2 / (4 * D * t0)))).to(dev)
+        B, Cc = torch.empty_like(A), torch.empty_like(A)
+        k = D / (12 * dx * dx)
+        dt = 1 / (2 * D * (3 / dx**2)) * 0.9
+        t = t0
+        while t < tFinal:
+            for stage, (src, dst) in enumerate(((A, B), (B, Cc), (Cc, B)), start=1):
+                a = _lib.StageArgs(target=adv.TARGETS["heat3d_sgpu_baseline"], flags=0, stage=stage, nx=n, ny=n, nzs=n, pitch=n,
+                                   k_begin=0, k_end=n, own_lo=3, own_hi=n - 3, k_global0=0,
+                                   dt=dt, dx=dx, dy=dx, dz=dx, kx=k, ky=k, kz=k)
+                _lib.check(adv.lib().adv_heat3d_stage_f64(C.byref(a), src.data_ptr(), A.data_ptr(), dst.data_ptr(), st))
+            A, B = B, A                     # the step's result is in B
+            if t + dt > tFinal:
+                dt = tFinal - t
+            t = t + dt
+        torch.cuda.synchronize()
+        err = np.abs(uE - A.cpu().numpy())
+        assert "%.2e" % (dx**3 * err.sum()) == "%.2e" % l1 and "%.2e" % err.max() == "%.2e" % linf, (n, dx**3 * err.sum(), err.max())

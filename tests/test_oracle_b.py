@@ -104,3 +104,30 @@ def test_oracle_b_reproduces_the_reference_accuracy_log_3d():
     for n, (l1, linf) in LOG_3D.items():
         g1, ginf = _accuracy_test(n, 3)
         assert _same_3_digits(g1, l1) and _same_3_digits(ginf, linf), (n, g1, ginf)
+
+
+def test_oracle_a_reproduces_the_3d_accuracy_log_too():
+    """Same table through the CUDA-program semantics (SingleGPU/Diffusion3d_baselineCode: same frame of 2, same
+    operator) stepped with the test's loop -- what tests/test_gpu_parity.py repeats on the GPU."""
+    import ctypes as C
+    f = orc.lib().orc_heat3d_step_f64
+    f.argtypes = [C.c_void_p] * 3 + [C.c_int] * 3 + [C.c_double] * 4 + [C.c_int]
+    for n, (l1, linf) in LOG_3D.items():
+        D, t0, L, tFinal = 1.0, 0.1, 10.0, 1.0
+        dx = L / (n - 1)
+        xs = -L / 2 + dx * np.arange(n)
+        X, Y, Z = np.meshgrid(xs, xs, xs, indexing="ij")
+        r2 = X**2 + Y**2 + Z**2
+        u = np.ascontiguousarray(np.exp(-r2 / (4 * D * t0)))
+        uE = (t0 / tFinal) ** 1.5 * np.exp(-r2 / (4 * D * tFinal))
+        uo, Lu = np.empty_like(u), np.zeros_like(u)
+        k = D / (12 * dx * dx)
+        dt = 1 / (2 * D * (3 / dx**2)) * 0.9
+        t = t0
+        while t < tFinal:
+            f(u.ctypes.data, uo.ctypes.data, Lu.ctypes.data, n, n, n, k, k, k, dt, 0)
+            if t + dt > tFinal:
+                dt = tFinal - t
+            t = t + dt
+        err = np.abs(uE - u)
+        assert _same_3_digits(dx**3 * err.sum(), l1) and _same_3_digits(err.max(), linf), n
