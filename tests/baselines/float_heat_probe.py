@@ -1,5 +1,5 @@
 import numpy as np, sys
-sys.path.insert(0, '.')
+sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__)))))
 import multigpu_advectiondiffusion_b200 as adv
 from oracle import oracle as orc
 h0 = orc.ic_heat3d_sgpu(32, 32, 32, dtype=np.float32)

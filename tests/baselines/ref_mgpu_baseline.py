@@ -7,7 +7,7 @@ Both programs time their own loop between barriers (`Kernel time ex. data transf
 reference synchronises the device before every RK launch, so at most one small kernel is still in flight when
 its clock stops.  result.bin of the two runs are compared (float32, whole padded array).  One JSON object.
 
-    python tools/ref_mgpu_baseline.py P        # P = number of GPUs / ranks
+    python tests/baselines/ref_mgpu_baseline.py P        # P = number of GPUs / ranks
 """
 import json
 import os
@@ -18,7 +18,7 @@ import tempfile
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 REF = os.path.join(ROOT, "oracle", "_ref")
 DRV = os.path.join(ROOT, "drivers")
 
