@@ -65,9 +65,9 @@ def test_no_cpu_fallback():
 
 def test_product_does_not_touch_the_oracle():
     """The oracle is test infrastructure: nothing under the package may import/link/exec it."""
-    pkg = os.path.join(ROOT, "multigpu_advectiondiffusion_b200")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".c", ".h", "Makefile")):
-                txt = open(os.path.join(dirpath, f), errors="replace").read()
-                assert "oracle" not in txt.lower().replace("no cpu", ""), os.path.join(dirpath, f)
+    for top in ("multigpu_advectiondiffusion_b200", "drivers", "include", "tools"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".c", ".h", ".sh", "Makefile")):
+                    txt = open(os.path.join(dirpath, f), errors="replace").read()
+                    assert "oracle" not in txt.lower().replace("no cpu", ""), os.path.join(dirpath, f)
