@@ -139,6 +139,11 @@ int  adv_step(adv_solver* s, int nsteps);
  * main.cpp:127-136); for ADV_TARGET_HEAT3D_MGPU tEnd = dt*iters (main.c:68).  max_steps < 0:
  * unbounded.  Returns the last dt, the step count and the reached time. */
 int  adv_run_until(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached);
+/* SURVEY 8f-2, no counterpart in the reference's CUDA programs: the same loop with the time step of its Matlab
+ * prototype, dt = CFL*dx/max|u| recomputed before every step (LFWENO5FDM3d.m:71) instead of the drivers'
+ * max|u| = 1 (main.c:193); max over every stored cell of the slab, one reduction pass + one 8-byte device-to-host
+ * read per step.  Burgers targets, single rank (nranks == 1) for now. */
+int  adv_run_until_cfl(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached);
 int  adv_sync(adv_solver* s);
 /* device time (ms) spent in the last adv_step/adv_run_until call, measured with CUDA events on
  * the solver's compute stream; valid after adv_sync */

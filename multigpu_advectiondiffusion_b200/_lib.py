@@ -66,6 +66,7 @@ SIGNATURES = {
     "adv_init_reference_ic": (C.c_int, [_P]),
     "adv_step": (C.c_int, [_P, C.c_int]),
     "adv_run_until": (C.c_int, [_P, C.c_double, C.c_int] + [C.POINTER(C.c_double)] * 3),
+    "adv_run_until_cfl": (C.c_int, [_P, C.c_double, C.c_int] + [C.POINTER(C.c_double)] * 3),
     "adv_sync": (C.c_int, [_P]),
     "adv_last_elapsed_ms": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "adv_kernel_launches": (C.c_longlong, [_P]),

@@ -15,6 +15,7 @@
 
 #include "burgers_kernels.cuh"
 #include "burgers2d_kernels.cuh"
+#include "reduce.cuh"
 #include "common.cuh"
 #include "halo.cuh"
 #include "heat_kernels.cuh"
@@ -977,6 +978,57 @@ extern "C" int adv_run_until(adv_solver* s, double tEnd, int max_steps, double* 
                          : run_until_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
     if (rc) return rc;
     if (s->d.nranks > 1) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
+    return ADV_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// the prototype's dynamic time step.  dt = CFL*dx/max|u| is recomputed before every step from one
+// reduction pass over the current field (LFWENO5FDM3d.m:71); the CUDA drivers of the reference fix max|u| = 1
+// (main.c:193), which adv_run_until reproduces.  The 8-byte result crosses to the host once per step.
+// ------------------------------------------------------------------------------------------
+template <typename REAL>
+static int run_until_cfl_impl(adv_solver* s, double tEnd_d, int max_steps, double* dt_last, double* steps, double* t_reached)
+{
+    unsigned long long* d_max = (unsigned long long*)(s->arena + s->off_flags + 256);      // spare words of the flag block
+    const REAL tEnd = (REAL)tEnd_d, CFL = (REAL)s->d.coef, dx = (REAL)s->dx;
+    const long long rows = (long long)s->urows * s->nzs;
+    const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+    REAL dt = 0, it = 0, t = 0;
+    while (t < tEnd && (max_steps < 0 || it < max_steps)) {
+        CUDA_TRY(cudaMemsetAsync(d_max, 0, sizeof(unsigned long long), s->stream));
+        absmax_kernel<REAL><<<grid, 256, 0, s->stream>>>((const REAL*)s->buf[s->cur], s->d.nx, (long long)s->pitch, rows, d_max);
+        CUDA_TRY(cudaGetLastError());
+        s->launches++;
+        unsigned long long bits = 0;
+        CUDA_TRY(cudaMemcpyAsync(&bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, s->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+        double umax_d;
+        memcpy(&umax_d, &bits, sizeof(umax_d));
+        const REAL umax = (REAL)umax_d;                     // exact: the reduction widened REAL values
+        dt = CFL * dx / umax;
+        if ((t + dt) > tEnd) { dt = tEnd - t; }
+        t += dt; it += 1;
+        int rc = do_step(s, (double)dt);
+        if (rc) return rc;
+    }
+    if (dt_last) *dt_last = dt;
+    if (steps) *steps = it;
+    if (t_reached) *t_reached = t;
+    return ADV_OK;
+}
+
+extern "C" int adv_run_until_cfl(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_run_until_cfl before adv_upload");
+    if (is_heat(s->d.target)) return fail(ADV_ERR_INVALID, "the dynamic CFL step applies to the Burgers targets");
+    if (s->d.nranks > 1) return fail(ADV_ERR_INVALID, "adv_run_until_cfl needs nranks == 1 (the max|u| all-reduce across ranks is not wired yet)");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    CUDA_TRY(cudaEventRecord(s->ev_start, s->stream));
+    int rc = s->esz == 8 ? run_until_cfl_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
+                         : run_until_cfl_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
+    if (rc) return rc;
     CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
     return ADV_OK;
 }

@@ -115,6 +115,12 @@ class Solver:
         check(lib().adv_run_until(self._h, tEnd, max_steps, C.byref(dt), C.byref(it), C.byref(t)))
         return dict(dt=dt.value, it=it.value, t=t.value)
 
+    def run_until_cfl(self, tEnd, max_steps=-1):
+        """dt = CFL*dx/max|u| recomputed every step (the Matlab prototype's time step; Burgers targets, one rank)."""
+        dt, it, t = C.c_double(), C.c_double(), C.c_double()
+        check(lib().adv_run_until_cfl(self._h, tEnd, max_steps, C.byref(dt), C.byref(it), C.byref(t)))
+        return dict(dt=dt.value, it=it.value, t=t.value)
+
     def sync(self):
         check(lib().adv_sync(self._h))
 

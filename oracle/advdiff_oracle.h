@@ -28,6 +28,7 @@ extern "C" {
 void orc_burgers3d_mgpu_rhs_##S(const REAL* u, REAL* Lu, int nx, int ny, int NZ, REAL dx, REAL dy, REAL dz); \
 int  orc_burgers3d_mgpu_step_##S(REAL* u, REAL* uo, REAL* Lu, int nx, int ny, int NZ, REAL dx, REAL dy, REAL dz, REAL dt); \
 int  orc_burgers3d_mgpu_run_##S(REAL* u, int nx, int ny, int nz_phys, REAL L, REAL W, REAL H, REAL CFL, REAL tEnd, int max_steps, double* dt_out, double* it_out, double* t_out); \
+int  orc_burgers3d_mgpu_run_cfl_##S(REAL* u, int nx, int ny, int nz_phys, REAL L, REAL W, REAL H, REAL CFL, REAL tEnd, int max_steps, double* dt_out, double* it_out, double* t_out); \
 int  orc_burgers3d_sgpu_step_##S(REAL* u, REAL* uo, REAL* Lu, int nx, int ny, int nz, REAL dx, REAL dy, REAL dz, REAL kx, REAL ky, REAL kz, REAL dt, int visc_quirk); \
 int  orc_burgers3d_sgpu_run_##S(REAL* u, int nx, int ny, int nz, REAL L, REAL W, REAL H, REAL CFL, REAL tEnd, int visc_quirk, int max_steps, double* dt_out, double* it_out, double* t_out); \
 int  orc_heat3d_step_##S(REAL* u, REAL* uo, REAL* Lu, int nx, int ny, int nz, REAL kx, REAL ky, REAL kz, REAL dt, int variant); \

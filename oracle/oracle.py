@@ -117,6 +117,19 @@ def burgers3d_mgpu(u0, tEnd, CFL=0.3, L=2.0, W=2.0, H=2.0, max_steps=-1):
     return u, dict(dt=dt.value, it=it.value, t=t.value)
 
 
+def burgers3d_mgpu_cfl(u0, tEnd, CFL=0.3, L=2.0, W=2.0, H=2.0, max_steps=-1):
+    """burgers3d_mgpu with dt = CFL*dx/max|u| recomputed every step (the Matlab prototype's time step)."""
+    s, R = _sfx(u0.dtype)
+    u = np.array(u0, copy=True, order="C")
+    NZ, ny, nx = u.shape
+    f = getattr(lib(), "orc_burgers3d_mgpu_run_cfl_" + s)
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, R, R, R, R, R, C.c_int] + [C.POINTER(C.c_double)] * 3
+    dt, it, t = C.c_double(), C.c_double(), C.c_double()
+    rc = f(_ptr(u), nx, ny, NZ - 6, L, W, H, CFL, tEnd, max_steps, C.byref(dt), C.byref(it), C.byref(t))
+    assert rc == 0
+    return u, dict(dt=dt.value, it=it.value, t=t.value)
+
+
 def burgers3d_sgpu(u0, tEnd, CFL=0.3, L=2.0, W=2.0, H=2.0, visc_quirk=1, max_steps=-1):
     s, R = _sfx(u0.dtype)
     u = np.array(u0, copy=True, order="C")

@@ -286,3 +286,24 @@ def test_gpu_reproduces_the_reference_accuracy_log_3d():
         torch.cuda.synchronize()
         err = np.abs(uE - A.cpu().numpy())
         assert "%.2e" % (dx**3 * err.sum()) == "%.2e" % l1 and "%.2e" % err.max() == "%.2e" % linf, (n, dx**3 * err.sum(), err.max())
+
+
+def test_dynamic_cfl_time_step_vs_oracle():
+    """adv_run_until_cfl: dt = CFL*dx/max|u| recomputed every step from a device reduction."""
+    nx, ny, nz = 40, 36, 32
+    u0 = 0.8 * orc.ic_burgers3d_mgpu(nx, ny, nz)
+    tEnd = 0.15                     # 8 dynamic steps (the last one 0.0139 long, far from a borderline count), 10 fixed ones
+    want, wi = orc.burgers3d_mgpu_cfl(u0, tEnd)
+    _, fixed = orc.burgers3d_mgpu(u0, tEnd)
+    with adv.Solver("burgers3d_mgpu", nx, ny, nz, coef=0.3) as s:
+        s.upload(u0)
+        gi = s.run_until_cfl(tEnd)
+        got = s.download()
+    got[:3], got[-3:] = u0[:3], u0[-3:]
+    assert gi["it"] == wi["it"] == 8 and fixed["it"] == 10
+    assert abs(gi["t"] - tEnd) < 1e-12 and abs(gi["dt"] / wi["dt"] - 1) < 1e-9
+    assert rel(got, want) <= 1e-11
+    with adv.Solver("heat3d_mgpu", nx, ny, nz, coef=1.0) as h:
+        h.upload(u0)
+        with pytest.raises(adv.AdvError):
+            h.run_until_cfl(0.01)

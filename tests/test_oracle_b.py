@@ -131,3 +131,17 @@ def test_oracle_a_reproduces_the_3d_accuracy_log_too():
             t = t + dt
         err = np.abs(uE - u)
         assert _same_3_digits(dx**3 * err.sum(), l1) and _same_3_digits(err.max(), linf), n
+
+
+def test_dynamic_cfl_step_a_vs_b():
+    """dt = CFL*dx/max|u| (LFWENO5FDM3d.m:71): Oracle A's variant (the checker of adv_run_until_cfl) against the
+    prototype transcription; the maximum sits at the pulse's peak, far from either boundary treatment."""
+    nx, ny, nz, steps = 56, 52, 50, 2
+    g = 0.8 * orc.ic_burgers3d_mgpu(nx, ny, nz)
+    a, ai = orc.burgers3d_mgpu_cfl(g, 1e9, max_steps=steps)
+    b, bi = orc.mlb_burgers3d(g, 1e9, CFL=0.3, dx=2.0 / (nx - 1), dy=2.0 / (ny - 1), dz=2.0 / (nz - 1), dynamic_dt=True, max_steps=steps)
+    _, fixed = orc.burgers3d_mgpu(g, 1e9, max_steps=steps)
+    assert ai["it"] == bi["it"] == steps and abs(ai["t"] / bi["t"] - 1) < 1e-14
+    assert ai["t"] > 1.2 * fixed["t"]            # max|u| = 0.8 < 1: longer steps than the drivers' fixed dt
+    m = 3 + 9 * steps
+    assert np.abs(a - b)[m:-m, m:-m, m:-m].max() / np.abs(a).max() <= TOL

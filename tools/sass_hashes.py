@@ -1,0 +1,36 @@
+#!/usr/bin/env python
+"""Per-kernel hash of the SASS in libadvdiff.so (addresses stripped).  Used to show that a change which only ADDS
+code paths leaves every already-validated kernel bit-identical:
+    python tools/sass_hashes.py > /tmp/before.json;  <edit, rebuild>;  python tools/sass_hashes.py /tmp/before.json"""
+import hashlib
+import json
+import os
+import re
+import subprocess
+import sys
+
+LIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "multigpu_advectiondiffusion_b200", "libadvdiff.so")
+
+
+def hashes():
+    out = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
+    funcs, cur = {}, None
+    for ln in out.splitlines():
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            cur = m.group(1)
+            funcs[cur] = []
+        elif cur and "/*" in ln:
+            funcs[cur].append(re.sub(r"/\*[0-9a-f]{4,}\*/", "", ln).strip())
+    return {k: hashlib.md5("\n".join(v).encode()).hexdigest() for k, v in funcs.items()}
+
+
+if __name__ == "__main__":
+    new = hashes()
+    if len(sys.argv) > 1:
+        old = json.load(open(sys.argv[1]))
+        print("kernels: %d -> %d" % (len(old), len(new)))
+        print("changed:", [k for k in old if new.get(k) != old[k]])
+        print("added:", [k for k in new if k not in old])
+    else:
+        print(json.dumps(new, indent=0))
