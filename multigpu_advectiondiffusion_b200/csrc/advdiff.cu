@@ -224,6 +224,41 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     return ADV_OK;
 }
 
+// EXPERIMENTAL (ADV_HEAT2D_TMA=1, off by default; written after this round's GPU time was spent and not yet run
+// on hardware): the 3-D TMA pipeline applied to a 2-D field seen as nx x 1 x rows -- one consumer warp and one
+// producer lane per 64-column strip, 8 rows in flight per strip.  Same arithmetic as heat2d_stage_rows.
+template <typename REAL>
+static int heat2d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h2d, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+{
+    constexpr int TY = 1, NST = 8;
+    typedef HeatTmaSmem<REAL, TY, NST, true> S;
+    const int rows_total = a->ny;
+    HeatArgs<REAL> h = h2d;
+    h.ny = 1; h.nzs = rows_total; h.plane = h.pitch;
+    h.lap = Box3{{h2d.lap.lo[0], 0, h2d.lap.lo[1]}, {h2d.lap.hi[0], 0, h2d.lap.hi[1]}};
+    h.rk = Box3{{h2d.rk.lo[0], 0, h2d.rk.lo[1]}, {h2d.rk.hi[0], 0, h2d.rk.hi[1]}};
+    h.kz = h2d.ky; h.ky = REAL(0); h.iso = 0;
+    CUtensorMap tm, tmo;
+    int rc = encode_tmap3(&tm, sizeof(REAL), u_in, a->nx, 1, rows_total, a->pitch, S::BX, S::BY);
+    if (rc) return rc;
+    rc = encode_tmap3(&tmo, sizeof(REAL), a->stage == 1 ? u_in : uo, a->nx, 1, rows_total, a->pitch, S::TX, TY);
+    if (rc) return rc;
+    const int rows = h.ke - h.kb, gx = (a->nx + S::TX - 1) / S::TX;
+    int nch = (8 * 1184 + gx - 1) / gx;                 // ~8 waves of 8 resident strips per SM
+    if (nch > rows / 32) nch = rows / 32;               // chunks of >= 32 rows (4 run-in rows each)
+    if (nch < 1) nch = 1;
+    const int chunk = (rows + nch - 1) / nch;
+    dim3 grid(gx, 1, (rows + chunk - 1) / chunk), block(32, TY + 1, 1);
+    const size_t shm = sizeof(S);
+#define HEAT2D_TMA_LAUNCH(STAGE_) do { \
+        auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_, true>; \
+        kfn<<<grid, block, shm, st>>>(tm, tmo, h, chunk, u_out); } while (0)
+    if (a->stage == 1) HEAT2D_TMA_LAUNCH(1); else if (a->stage == 2) HEAT2D_TMA_LAUNCH(2); else HEAT2D_TMA_LAUNCH(3);
+#undef HEAT2D_TMA_LAUNCH
+    CUDA_TRY(cudaGetLastError());
+    return ADV_OK;
+}
+
 template <typename REAL>
 static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st, PeerOut peer = kNoPeer)
 {
@@ -243,6 +278,10 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     const size_t vb = 2 * sizeof(REAL);
     const bool vec_ok = a->pitch % 2 == 0 && (uintptr_t)u_in % vb == 0 && (uintptr_t)u_out % vb == 0 && (a->stage == 1 || (uintptr_t)uo % vb == 0) &&
                         (!peer.out2 || ((uintptr_t)peer.out2 % vb == 0 && peer.off2 % 2 == 0));
+    static const bool heat2d_tma = getenv("ADV_HEAT2D_TMA") != nullptr;     // experimental, see heat2d_launch_tma
+    if (heat2d_tma && vec_ok && a->nx % 2 == 0 && a->nx >= 8 && a->pitch % (16 / sizeof(REAL)) == 0 &&
+        (uintptr_t)u_in % 16 == 0 && (uintptr_t)u_out % 16 == 0 && (a->stage == 1 || (uintptr_t)uo % 16 == 0) && get_tmap_encode())
+        return heat2d_launch_tma<REAL>(a, h, u_in, uo, u_out, st);
     // pairs-of-cells row-marching kernel for slabs and large grids; one-thread-per-cell kernel for the small
     // single-GPU case (512^2 lives in L2 and is launch-bound) and for unaligned caller buffers
     if (vec_ok && (slab || (size_t)a->nx * a->ny > ((size_t)1 << 21))) {

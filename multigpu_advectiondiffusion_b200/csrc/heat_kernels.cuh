@@ -217,11 +217,15 @@ __device__ __forceinline__ void mbar_arrive_(unsigned bar)
     asm volatile("{\n.reg .b64 st;\nmbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(bar) : "memory");
 }
 
-template <typename REAL, int TY, int NST>
+// TWO_D: the same pipeline for a 2-D field seen as nx x 1 x rows -- the marching axis is the 2-D y, the tile has
+// one row (TY = 1) and no y halo, the Laplacian is kx*X + kz*Z with the 2-D ky passed as kz (same operand order
+// as heat2d_stage_rows, so the two kernels give the same bits).
+template <typename REAL, int TY, int NST, bool TWO_D = false>
 struct HeatTmaSmem {
     static constexpr int TX = 64, H = 2;
+    static constexpr int HY = TWO_D ? 0 : H;
     static constexpr int HX = (sizeof(REAL) == 8) ? 2 : 4;
-    static constexpr int BX = TX + 2 * HX, BY = TY + 2 * H;
+    static constexpr int BX = TX + 2 * HX, BY = TY + 2 * HY;
     struct alignas(128) Plane { REAL v[BY][BX]; };
     struct alignas(128) Tile { REAL v[TY][TX]; };
     Plane stage[NST];
@@ -229,14 +233,14 @@ struct HeatTmaSmem {
     unsigned long long full[NST], empty[NST];
 };
 
-template <typename REAL, int TY, int NST, int STAGE>
+template <typename REAL, int TY, int NST, int STAGE, bool TWO_D = false>
 __global__ void __launch_bounds__(32 * (TY + 1))
 heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_uo,
                   HeatArgs<REAL> a, int chunk, REAL* __restrict__ out)
 {
     typedef typename Vec2T<REAL>::type V2;
-    typedef HeatTmaSmem<REAL, TY, NST> S;
-    constexpr int TX = S::TX, H = S::H, HX = S::HX, BX = S::BX, BY = S::BY;
+    typedef HeatTmaSmem<REAL, TY, NST, TWO_D> S;
+    constexpr int TX = S::TX, H = S::HY, HX = S::HX, BX = S::BX, BY = S::BY;
     constexpr unsigned kBytesU = BX * BY * sizeof(REAL), kBytesO = TX * TY * sizeof(REAL);
     extern __shared__ __align__(128) unsigned char heat_smem_raw[];
     S& sm = *reinterpret_cast<S*>(heat_smem_raw);
@@ -290,6 +294,13 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     auto lap = [&](const V2& zm2, const V2& zm1, const V2& zc, const V2& zp1, const V2& zp2, const REAL* row, V2& Lu) {
         const V2 xl = *reinterpret_cast<const V2*>(row - 2), xr = *reinterpret_cast<const V2*>(row + 2);
+        if (TWO_D) {
+            Lu.x = a.kx * (-xl.x + REAL(16) * xl.y - REAL(30) * zc.x + REAL(16) * zc.y - xr.x) +
+                   a.kz * (-zm2.x + REAL(16) * zm1.x - REAL(30) * zc.x + REAL(16) * zp1.x - zp2.x);
+            Lu.y = a.kx * (-xl.y + REAL(16) * zc.x - REAL(30) * zc.y + REAL(16) * xr.x - xr.y) +
+                   a.kz * (-zm2.y + REAL(16) * zm1.y - REAL(30) * zc.y + REAL(16) * zp1.y - zp2.y);
+            return;
+        }
         const V2 ym2 = *reinterpret_cast<const V2*>(row - 2 * BX), ym1 = *reinterpret_cast<const V2*>(row - BX);
         const V2 yp1 = *reinterpret_cast<const V2*>(row + BX), yp2 = *reinterpret_cast<const V2*>(row + 2 * BX);
         if (a.iso) {

@@ -1,0 +1,54 @@
+#!/usr/bin/env python
+"""Manual bring-up check for the EXPERIMENTAL 2-D TMA heat path (ADV_HEAT2D_TMA=1, csrc/advdiff.cu
+heat2d_launch_tma): not part of the pytest suite because the kernel instantiation has never run on hardware.
+Run it under a timeout on a GPU box:
+
+    timeout -s KILL 120 python tests/baselines/heat2d_tma_check.py
+
+It runs the same problems through the default kernel and the experimental one (separate processes: the switch is
+read once per process), expects bit-identical fields, parity with the oracle, and prints both rates."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+
+CHILD = r'''
+import sys, json, time, numpy as np
+sys.path.insert(0, %r)
+import multigpu_advectiondiffusion_b200 as adv
+from oracle import oracle as orc
+out = {}
+for nx, ny in ((64, 64), (400, 400), (130, 77), (1030, 48)):
+    u0 = orc.ic_heat2d_mgpu(nx, ny) + np.random.default_rng(5).random((ny + 6, nx))
+    want, wi = orc.heat2d_mgpu(u0, 25)
+    got, gi = adv.solve_host("heat2d_mgpu", u0, wi["dt"] * 25, coef=1.0)
+    out["%%dx%%d" %% (nx, ny)] = dict(rel=orc.rel_err(got, want), it=gi["it"], sum=float(got.sum()), crc=int(np.frombuffer(got.tobytes(), dtype=np.uint32).sum()))
+with adv.Solver("heat2d_mgpu", 8192, 8192, coef=1.0) as s:
+    s.init_reference_ic(); s.step(3); s.sync(); s.step(20); s.sync()
+    out["rate_8192"] = 8192 * 8192 * 3 * 20 / (s.elapsed_ms() * 1e-3) / 1e6
+print("RESULT " + json.dumps(out))
+''' % ROOT
+
+
+def run(env_extra):
+    r = subprocess.run([sys.executable, "-c", CHILD], capture_output=True, text=True, timeout=100, env=dict(os.environ, **env_extra))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("RESULT ")][0][7:])
+
+
+if __name__ == "__main__":
+    base = run({})
+    tma = run({"ADV_HEAT2D_TMA": "1"})
+    for k in base:
+        if k.startswith("rate"):
+            print("%s: default %.0f, ADV_HEAT2D_TMA=1 %.0f Mcell-updates/s" % (k, base[k], tma[k]))
+        else:
+            same = base[k]["crc"] == tma[k]["crc"] and base[k]["sum"] == tma[k]["sum"]
+            print(k, "rel err default %.2e tma %.2e" % (base[k]["rel"], tma[k]["rel"]), "bit-identical" if same else "DIFFERENT")
+            assert tma[k]["rel"] <= 1e-12 and same
+    print("heat2d TMA path OK")

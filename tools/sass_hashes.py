@@ -30,7 +30,8 @@ if __name__ == "__main__":
     if len(sys.argv) > 1:
         old = json.load(open(sys.argv[1]))
         print("kernels: %d -> %d" % (len(old), len(new)))
-        print("changed:", [k for k in old if new.get(k) != old[k]])
+        print("changed (same name, different SASS):", [k for k in old if k in new and new[k] != old[k]])
+        print("old kernels whose SASS exists under no name any more:", [k for k, v in old.items() if v not in set(new.values())])
         print("added:", [k for k in new if k not in old])
     else:
         print(json.dumps(new, indent=0))
