@@ -71,3 +71,38 @@ def test_product_does_not_touch_the_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".c", ".h", ".sh", "Makefile")):
                     txt = open(os.path.join(dirpath, f), errors="replace").read()
                     assert "oracle" not in txt.lower().replace("no cpu", ""), os.path.join(dirpath, f)
+
+
+def test_descriptor_validation_needs_no_device():
+    """adv_create refuses bad descriptors before it looks for a GPU (host logic of the boundary): too-small grids,
+    slabs that do not divide or are thinner than 2*RADIUS, rank outside the communicator, slabs on a single-GPU
+    target, non-positive C/K/CFL, unknown target / precision."""
+    cases = [
+        (("burgers3d_mgpu", 4, 4, 4), {}, "small"),
+        (("heat3d_mgpu", 32, 32, 5), {}, "small"),
+        (("burgers3d_mgpu", 32, 32, 30), dict(nranks=4, rank=0), "divisible"),
+        (("burgers3d_mgpu", 32, 32, 16), dict(nranks=4, rank=0), "thinner"),
+        (("burgers3d_mgpu", 32, 32, 32), dict(nranks=2, rank=2), "rank"),
+        (("heat3d_sgpu_baseline", 32, 32, 32), dict(nranks=2, rank=0), "MGPU"),
+        (("burgers2d_mgpu", 64, 50, 1), dict(nranks=4, rank=0), "divisible"),
+        (("heat2d_mgpu", 64, 16, 1), dict(nranks=4, rank=1), "thinner"),
+        (("burgers3d_mgpu", 32, 32, 32), dict(coef=0.0), "positive"),
+        ((99, 32, 32, 32), {}, "target"),
+        (("burgers3d_mgpu", 32, 32, 32), dict(precision=7), "precision"),
+    ]
+    for args, kw, word in cases:
+        with pytest.raises(adv.AdvError) as e:
+            adv.Solver(*args, **kw)
+        assert e.value.code == 1 and word in str(e.value), (args, kw, str(e.value))
+
+
+def test_null_and_state_errors_need_no_device():
+    L = adv.lib()
+    assert L.adv_create(None, None) == 1 and b"NULL" in L.adv_last_error()
+    assert L.adv_step(None, 1) == 1 and L.adv_run_until_cfl(None, 1.0, -1, None, None, None) == 1
+    assert L.adv_local_elems(None) == 0 and L.adv_dt(None) == 0.0 and L.adv_halo_mode(None) == 0
+    a = _lib.StageArgs(target=adv.TARGETS["burgers3d_mgpu"], stage=4, nx=32, ny=32, nzs=38, pitch=32)
+    buf = (C.c_double * 8)()
+    assert L.adv_burgers3d_stage_f64(C.byref(a), buf, buf, buf, buf, None) == 1 and b"stage" in L.adv_last_error()
+    a.stage = 2
+    assert L.adv_burgers3d_stage_f64(C.byref(a), buf, buf, buf, buf, None) == 1 and b"alias" in L.adv_last_error()
