@@ -122,6 +122,49 @@ def run_cpu2d(rank, P, nx, ny, nsteps):
         print("MP_OK cpu2d P=%d bit-exact vs oracle" % P)
 
 
+def run_cpu_heat2d(rank, P, nx, ny, nsteps):
+    """y-slab heat (MultiGPU/Diffusion2d_Baseline): the Laplacian rows of a slab are its owned rows, plus pad row 2
+    on the FIRST slab only (Compute_Laplace's jstart-1 offset, Kernels.cu:144) -- the rule libadvdiff applies
+    through k_global0 == 0.  numpy arithmetic in the reference's operand order; bit-exact against the oracle."""
+    g = orc.ic_heat2d_mgpu(nx, ny) + np.random.default_rng(9).random((ny + 6, nx))
+    dx, dy = 2.0 / (nx - 1), 2.0 / (ny - 1)
+    dt = 1 / (2 * 1.0 * (1 / dx / dx + 1 / dy / dy)) * 0.8
+    kx, ky = 1.0 / (12 * dx * dx), 1.0 / (12 * dy * dy)
+    g0, g1 = slab_bounds(ny, P, rank)
+    u = g[g0:g1].copy()
+    nys = u.shape[0]
+    jlo = 3 - (1 if rank == 0 else 0)
+    for _ in range(nsteps):
+        uo = u.copy()
+        for stage in (1, 2, 3):
+            Lu = np.zeros_like(u)
+            c = u[jlo:nys - 3, 3:nx - 3]
+            Lu[jlo:nys - 3, 3:nx - 3] = (
+                kx * (-u[jlo:nys - 3, 1:nx - 5] + 16 * u[jlo:nys - 3, 2:nx - 4] - 30 * c + 16 * u[jlo:nys - 3, 4:nx - 2] - u[jlo:nys - 3, 5:nx - 1]) +
+                ky * (-u[jlo - 2:nys - 5, 3:nx - 3] + 16 * u[jlo - 1:nys - 4, 3:nx - 3] - 30 * c + 16 * u[jlo + 1:nys - 2, 3:nx - 3] - u[jlo + 2:nys - 1, 3:nx - 3]))
+            if stage == 1:
+                new = uo + dt * Lu
+            elif stage == 2:
+                new = 0.75 * uo + 0.25 * (u + dt * Lu)
+            else:
+                new = (uo + 2 * (u + dt * Lu)) / 3
+            lo = 0 if rank == 0 else 3
+            hi = nys if rank == P - 1 else nys - 3
+            u[lo:hi] = new[lo:hi]
+            exchange_cpu(u, rank, P)
+    parts = [None] * P if rank == 0 else None
+    dist.gather_object(u, parts, dst=0)
+    if rank == 0:
+        merged = g.copy()
+        nyl = ny // P
+        for r in range(P):
+            merged[r * nyl + 3: r * nyl + 3 + nyl] = parts[r][3:3 + nyl]
+        want, wi = orc.heat2d_mgpu(g, nsteps)
+        assert wi["it"] == nsteps
+        assert np.array_equal(merged, want), float(np.abs(merged - want).max())
+        print("MP_OK cpu_heat2d P=%d bit-exact vs oracle" % P)
+
+
 def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
     import multigpu_advectiondiffusion_b200 as adv
     torch.cuda.set_device(rank)
@@ -188,6 +231,7 @@ def main():
         if mode == "cpu":
             run_cpu(rank, P, 20, 22, 24, 2)
             run_cpu2d(rank, P, 30, 48, 3)
+            run_cpu_heat2d(rank, P, 34, 48, 4)
         else:
             for halo in ("nccl", "peer"):
                 for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5),

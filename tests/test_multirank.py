@@ -20,12 +20,12 @@ def _launch(mode, nproc, port):
 
 def test_cpu_gloo_two_ranks():
     r = _launch("cpu", 2, 29731)
-    assert r.returncode == 0 and "MP_OK cpu P=2" in r.stdout and "MP_OK cpu2d P=2" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.returncode == 0 and "MP_OK cpu P=2" in r.stdout and "MP_OK cpu2d P=2" in r.stdout and "MP_OK cpu_heat2d P=2" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_cpu_gloo_four_ranks():
     r = _launch("cpu", 4, 29732)
-    assert r.returncode == 0 and "MP_OK cpu P=4" in r.stdout and "MP_OK cpu2d P=4" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.returncode == 0 and "MP_OK cpu P=4" in r.stdout and "MP_OK cpu2d P=4" in r.stdout and "MP_OK cpu_heat2d P=4" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 @pytest.mark.gpu
