@@ -145,3 +145,34 @@ def test_dynamic_cfl_step_a_vs_b():
     assert ai["t"] > 1.2 * fixed["t"]            # max|u| = 0.8 < 1: longer steps than the drivers' fixed dt
     m = 3 + 9 * steps
     assert np.abs(a - b)[m:-m, m:-m, m:-m].max() / np.abs(a).max() <= TOL
+
+
+def test_accuracy_log_1d_table_too():
+    """The 1-D table of the same log (diffusion1dTest.m + Laplace1d.m; not on the hot path, transcribed in numpy
+    here only to show that the recovered parameters explain the WHOLE log: 24 of 24 numbers)."""
+    log_1d = {10: (1.81e-01, 4.97e-02), 20: (4.87e-02, 1.34e-02), 40: (9.89e-03, 2.62e-03), 80: (1.50e-03, 8.34e-04)}
+    for n, (l1, linf) in log_1d.items():
+        D, t0, L, tFinal = 1.0, 0.1, 10.0, 1.0
+        dx = L / (n - 1)
+        x = -L / 2 + dx * np.arange(n)
+        Dx = D / dx**2
+        u = np.exp(-x**2 / (4 * D * t0))
+        uE = np.sqrt(t0 / tFinal) * np.exp(-x**2 / (4 * D * tFinal))
+        dt = 1 / (2 * D * (1 / dx**2)) * 0.9
+        t = t0
+
+        def lap(w):
+            d = np.zeros_like(w)
+            d[2:n - 2] = Dx / 12 * (-w[4:n] + 16 * w[3:n - 1] - 30 * w[2:n - 2] + 16 * w[1:n - 3] - w[0:n - 4])
+            return d
+        while t < tFinal:
+            uo = u.copy()
+            u = uo + dt * lap(u)
+            u = 0.75 * uo + 0.25 * (u + dt * lap(u))
+            u = (uo + 2 * (u + dt * lap(u))) / 3
+            u[0] = u[-1] = 0
+            if t + dt > tFinal:
+                dt = tFinal - t
+            t = t + dt
+        err = np.abs(uE - u)
+        assert _same_3_digits(dx * err.sum(), l1) and _same_3_digits(err.max(), linf), (n, dx * err.sum(), err.max())
