@@ -7,7 +7,9 @@ unnamed hardware, the ITERATION COUNT of each run -- known answers for the drive
     MultiGPU/Diffusion3d_Baseline/Run.m:4-14   400 x 200 x 206, 100 iterations asked  -> 101 x 3 (the extra step)
     MultiGPU/Diffusion2d_Baseline/Run.m:4-14   400 x 406,       1000 iterations asked -> 1001 x 3
 
-The counts depend only on the spacings, so the Burgers 3-D case uses a thin grid with the recorded nx."""
+    SingleGPU/Burgers3d_WENO5/Run.m:15-37      512^3 and 1000 x 1000 x 200, tEnd 0.10, CFL 0.30 -> 86 x 3 and 167 x 3
+
+The counts depend only on the spacings, so the Burgers 3-D cases use thin grids with the recorded nx."""
 import numpy as np
 import pytest
 
@@ -19,6 +21,9 @@ def test_oracle_reproduces_the_recorded_iteration_counts():
     assert i["it"] == 267 and i["t"] == 0.40
     _, i = orc.burgers2d_mgpu(orc.ic_burgers2d_mgpu(400, 400), 0.40, 0.40)
     assert i["it"] == 200
+    for nx, steps in ((512, 86), (1000, 167)):
+        _, i = orc.burgers3d_sgpu(orc.ic_burgers3d_sgpu(nx, 8, 8), 0.10, 0.30)
+        assert i["it"] == steps
     _, i = orc.heat2d_mgpu(orc.ic_heat2d_mgpu(400, 400), 1000)
     assert i["it"] == 1001
     _, i = orc.heat3d(orc.ic_heat3d_mgpu(400, 200, 200), 100, "mgpu", 1.0, 2.0, 2.0, 2.0)
