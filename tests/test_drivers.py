@@ -151,3 +151,18 @@ def test_mgpu_drivers_on_two_gpus_match_the_oracle(tmp_path):
     res = run("Diffusion2d_mgpu.run", [1.0, 2.0, 2.0, nx, ny, 40, 32, 32])
     want, _ = orc.heat2d_mgpu(orc.ic_heat2d_mgpu(nx, ny), 40)
     assert np.abs(res - want.astype(np.float32).ravel()).max() <= 1e-6
+
+
+def test_summary_arithmetic_reproduces_the_recorded_run_headers(tmp_path):
+    """The drivers print the reference's synthetic "Total effective GFLOPs" (updates x 8 / seconds, Tools.c:240-243,
+    tools.cpp:148-151).  Feeding the recorded kernel times of two Run.m headers through drivers/common.h gives the
+    recorded figures: SingleGPU/Diffusion3d_baselineCode/Run.m:3-12 (6.664205) and SingleGPU/Burgers3d_WENO5/
+    Run.m:15-25 (7.036459).  The heat header's "Final Time 0.329157" is t0 + 605 dt of that driver's dt formula."""
+    src = tmp_path / "g.c"
+    src.write_text('#include "common.h"\nconst char* adv_last_error(void){return "";}\nint main(void){printf("%lf %lf\\n", calc_gflops_steps(5.81f, 605, 201, 199, 200),'
+                   ' calc_gflops_stages(39.37f, 86, 512, 512, 512)); return 0;}\n')
+    exe = tmp_path / "g"
+    subprocess.check_call(["gcc", "-I", DRV, "-I", os.path.join(ROOT, "include"), "-Wno-unused-function", str(src), "-o", str(exe)])
+    assert subprocess.check_output([str(exe)], text=True).split() == ["6.664205", "7.036459"]
+    _, info = orc.heat3d(np.zeros((200, 199, 201)), 0, "baseline", 1.0, 10, 10, 10)
+    assert "%f" % (0.1 + 605 * info["dt"]) == "0.329157"
