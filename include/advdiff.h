@@ -231,8 +231,10 @@ int adv_burgers2d_stage_f32(const adv_stage_args* a, const float* u_in, const fl
  *  - Limit: pitch * nzs <= ADV_NOALLOC_MAX_ELEMS (9 MiB of doubles, enough for 1024 x (1024+6) planes);
  *    larger fields are refused with ADV_ERR_INVALID and a message -- use the rowacc variant for them.
  *  - Every GPU that loads the library carries those 9 MiB until the process exits.
- *  - The first call on each device looks up the array's device address (with that device current, i.e.
- *    the device the stream belongs to).  Make that first call before starting any stream capture.
+ *  - The first call on each device looks up the array's device address.  Make that first call before
+ *    starting any stream capture.  The device the stream belongs to must be the CURRENT device on every
+ *    call, not only the first (a mismatch is refused with ADV_ERR_INVALID); the looked-up addresses do not
+ *    survive cudaDeviceReset.  Host threads may call concurrently for different devices.
  *  - All calls on one device share the one array and it keeps what the last call left: stage 1 clears
  *    the rows of the planes [k_begin,k_end) it produces, stages 2 and 3 continue from stage 1 of the same step.  Two time steps in flight on
  *    the same GPU at once (different streams, or different fields interleaved stage by stage) race on it;

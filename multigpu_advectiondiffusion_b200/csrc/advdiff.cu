@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <new>
 #include <stdint.h>
 #include <thread>
@@ -46,6 +47,11 @@ static int fail(int code, const char* fmt, ...)
     } while (0)
 
 extern "C" const char* adv_last_error(void) { return g_err; }
+
+// A/B switches (ADV_* environment variables) are read at every call, not latched at first use: a caller or a
+// test that sets one after the library has already launched something gets what it asked for.
+static bool env_on(const char* name) { return getenv(name) != nullptr; }
+static int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 extern "C" int adv_version(void) { return ADV_VERSION; }
 
 extern "C" int adv_device_count(int* count)
@@ -175,7 +181,7 @@ static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, c
     if (rc) return rc;
     const int planes = a->k_end - a->k_begin;
     const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + TY - 1) / TY;
-    static const int nch_env = getenv("ADV_HEAT_NCH") ? atoi(getenv("ADV_HEAT_NCH")) : 0;
+    const int nch_env = env_int("ADV_HEAT_NCH", 0);
     int nch = nch_env > 0 ? nch_env : (2368 + gx * gy - 1) / (gx * gy);
     if (nch > planes / 16) nch = planes / 16;
     if (nch < 1) nch = 1;
@@ -212,7 +218,7 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     if (rc) return rc;
     h.out2 = (REAL*)peer.out2; h.off2 = peer.off2;
     // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
-    static const int heat_variant = getenv("ADV_HEAT_DIRECT") ? 0 : 1;     // A/B switch: ADV_HEAT_DIRECT=1 forces the direct kernel
+    const int heat_variant = env_on("ADV_HEAT_DIRECT") ? 0 : 1;     // A/B switch: ADV_HEAT_DIRECT=1 forces the direct kernel
     const bool tma_ok = heat_variant > 0 && heat3d_tma_ok<REAL>(a, u_in, uo, u_out);
     if (peer.out2 && !tma_ok) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
     if (tma_ok) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);     // 64x8 tile, 6 planes in flight
@@ -278,7 +284,7 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     const size_t vb = 2 * sizeof(REAL);
     const bool vec_ok = a->pitch % 2 == 0 && (uintptr_t)u_in % vb == 0 && (uintptr_t)u_out % vb == 0 && (a->stage == 1 || (uintptr_t)uo % vb == 0) &&
                         (!peer.out2 || ((uintptr_t)peer.out2 % vb == 0 && peer.off2 % 2 == 0));
-    static const bool heat2d_tma = getenv("ADV_HEAT2D_TMA") != nullptr;     // experimental, see heat2d_launch_tma
+    const bool heat2d_tma = env_on("ADV_HEAT2D_TMA");     // experimental, see heat2d_launch_tma
     if (heat2d_tma && vec_ok && a->nx % 2 == 0 && a->nx >= 8 && a->pitch % (16 / sizeof(REAL)) == 0 &&
         (uintptr_t)u_in % 16 == 0 && (uintptr_t)u_out % 16 == 0 && (a->stage == 1 || (uintptr_t)uo % 16 == 0) && get_tmap_encode())
         return heat2d_launch_tma<REAL>(a, h, u_in, uo, u_out, st);
@@ -286,7 +292,7 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     // single-GPU case (512^2 lives in L2 and is launch-bound) and for unaligned caller buffers
     if (vec_ok && (slab || (size_t)a->nx * a->ny > ((size_t)1 << 21))) {
         const int rows = h.ke - h.kb, gx = (a->nx / 2 + 1 + 127) / 128;
-        static const int ctas_per_sm = getenv("ADV_HEAT2D_CTAS") ? atoi(getenv("ADV_HEAT2D_CTAS")) : 128;  // A/B switch; measured at 8192^2: 16 -> 184, 64 -> 239, 128 -> 253 Gcell-updates/s (equal-length CTAs: many waves keep the tail short)
+        const int ctas_per_sm = env_int("ADV_HEAT2D_CTAS", 128);  // A/B switch; measured at 8192^2: 16 -> 184, 64 -> 239, 128 -> 253 Gcell-updates/s (equal-length CTAs: many waves keep the tail short)
         int nch = (ctas_per_sm * 148 + gx - 1) / gx;        // many short chunks: loads in flight matter more than the 4 run-in rows ...
         if (nch > rows / 16) nch = rows / 16;               // ... but chunks of >= 16 rows (the 4 run-in rows are L2 hits: neighbouring chunks run together)
         if (nch < 1) nch = 1;
@@ -332,6 +338,13 @@ static int burgers2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     constexpr int TX = 64, TY = 16, NT = 256;
     dim3 grid((a->nx + TX - 1) / TX, (a->k_end - a->k_begin + TY - 1) / TY, 1), block(NT, 1, 1);
     const REAL* uo_ = a->stage == 1 ? u_in : uo;
+    if (env_on("ADV_BURGERS_DIRECT")) {     // parity anchor: reference operand order, one thread per cell
+        dim3 dblock(64, 4, 1), dgrid((a->nx + 63) / 64, (a->k_end - a->k_begin + 3) / 4, 1);
+        if (peer.out2) burgers2d_stage_direct<REAL, WENO_JS, true><<<dgrid, dblock, 0, st>>>(b, u_in, uo_, u_out);
+        else burgers2d_stage_direct<REAL, WENO_JS, false><<<dgrid, dblock, 0, st>>>(b, u_in, uo_, u_out);
+        CUDA_TRY(cudaGetLastError());
+        return ADV_OK;
+    }
     const size_t shm = sizeof(Burgers2dSmem<REAL>);
 #define LAUNCH_B2D(STAGE_, PEER_) do { \
         auto kfn = burgers2d_stage_tile<REAL, WENO_JS, STAGE_, PEER_>; \
@@ -375,7 +388,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     constexpr int CHUNK = 16;
     dim3 block(32, 4, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
-    static const bool force_direct = getenv("ADV_BURGERS_DIRECT") != nullptr;   // A/B switch for tests and profiling
+    const bool force_direct = env_on("ADV_BURGERS_DIRECT");   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
     if (!force_direct) {
         // ring kernel: 32x16 tile, 2 cells per thread, 8+1 warps, 2 CTAs/SM
@@ -931,6 +944,22 @@ static int do_stage(adv_solver* s, int stage, double dt, const void* in, const v
     return launch_stage(s, stage, dt, in, uo, out, ilo, ihi, s->stream);
 }
 
+// End of a run of steps on a multi-rank solver: make "this rank's stream is idle" imply "this rank's ghost
+// planes hold the neighbours' last stage".  NCCL path: wait for the comm stream's last exchange.  Peer-store
+// path: the neighbours write our ghost planes themselves, so wait until both have signalled the last stage
+// executed -- otherwise adv_download could return stale ghost planes and an adv_upload that follows could
+// overwrite freshly stored ones (the next step's flag wait would then pass on wrong data).
+static int halo_quiesce(adv_solver* s)
+{
+    if (s->d.nranks <= 1) return ADV_OK;
+    if (!s->p2p) { CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0)); return ADV_OK; }
+    int rc;
+    if (s->stage_counter == 0) return ADV_OK;
+    if (s->d.rank > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, s->stage_counter))) return rc;
+    if (s->d.rank < s->d.nranks - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, s->stage_counter))) return rc;
+    return ADV_OK;
+}
+
 static int do_step(adv_solver* s, double dt)
 {
     void* A = s->buf[s->cur];
@@ -950,7 +979,7 @@ extern "C" int adv_step(adv_solver* s, int nsteps)
     if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_step before adv_upload");
     if (nsteps < 0) return fail(ADV_ERR_INVALID, "nsteps < 0");
     CUDA_TRY(cudaSetDevice(s->d.device));
-    static const bool no_graph = getenv("ADV_NO_GRAPH") != nullptr;
+    const bool no_graph = env_on("ADV_NO_GRAPH");
     const size_t cells = (size_t)s->d.nx * s->urows * s->nzs;
     const bool use_graph = !no_graph && s->d.nranks == 1 && nsteps >= 12 && cells <= ((size_t)1 << 23);
     if (use_graph && !s->graph_exec) {
@@ -981,7 +1010,7 @@ extern "C" int adv_step(adv_solver* s, int nsteps)
         int rc = do_step(s, s->dt_fixed);
         if (rc) return rc;
     }
-    if (s->d.nranks > 1) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    { int rc = halo_quiesce(s); if (rc) return rc; }
     CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
     return ADV_OK;
 }
@@ -1016,7 +1045,7 @@ extern "C" int adv_run_until(adv_solver* s, double tEnd, int max_steps, double* 
     int rc = s->esz == 8 ? run_until_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
                          : run_until_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
     if (rc) return rc;
-    if (s->d.nranks > 1) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));
+    if ((rc = halo_quiesce(s))) return rc;
     CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
     return ADV_OK;
 }
@@ -1137,25 +1166,25 @@ static __device__ __align__(256) double g_noalloc_rowacc[ADV_NOALLOC_MAX_ELEMS];
 
 // In host code `g_noalloc_rowacc` is only a handle for the runtime, not an address the GPU can
 // use; the device address has to be asked for, once per device, with that device current.
-static double* noalloc_rowacc_for_current_device(int* rc_out)
+// The per-device slots are atomics: the C drivers run one host thread per GPU, and two threads may
+// make their first call at the same moment (both then look the address up and store the same value).
+// The cached addresses belong to the device's primary context: they do not survive cudaDeviceReset.
+static double* noalloc_rowacc_for_device(int dev, int* rc_out)
 {
     enum { MAX_DEV = 64 };
-    static double* ptr[MAX_DEV];            // zero-initialised; one slot per device ordinal
+    static std::atomic<double*> ptr[MAX_DEV];       // zero-initialised; one slot per device ordinal
     *rc_out = ADV_OK;
-    int dev = -1;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) { *rc_out = fail(ADV_ERR_NO_DEVICE, "cudaGetDevice: %s", cudaGetErrorString(e)); return nullptr; }
     if (dev < 0 || dev >= MAX_DEV) { *rc_out = fail(ADV_ERR_INVALID, "device ordinal %d not supported", dev); return nullptr; }
-    if (!ptr[dev]) {
-        double* p = nullptr;
-        e = cudaGetSymbolAddress((void**)&p, g_noalloc_rowacc);
+    double* p = ptr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_rowacc);
         if (e != cudaSuccess || !p) {
             *rc_out = fail(ADV_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
             return nullptr;
         }
-        ptr[dev] = p;
+        ptr[dev].store(p, std::memory_order_release);
     }
-    return ptr[dev];
+    return p;
 }
 
 extern "C" int adv_burgers3d_stage_f64_noalloc(const adv_stage_args* a, const double* u_in, const double* uo,
@@ -1171,10 +1200,21 @@ extern "C" int adv_burgers3d_stage_f64_noalloc(const adv_stage_args* a, const do
         return fail(ADV_ERR_INVALID, "field needs %llu scratch elements (pitch %zu x %d planes) but the built-in scratch holds "
                                      "%llu; use adv_burgers3d_stage_f64 with caller-provided scratch",
                     need, a->pitch, a->nzs, (unsigned long long)ADV_NOALLOC_MAX_ELEMS);
-    int rc;
-    double* scratch = noalloc_rowacc_for_current_device(&rc);
-    if (!scratch) return rc;
+    int rc, dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
     cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread) {
+        // the array whose address we hand to the kernel is the CURRENT device's copy: a stream of another
+        // device would run the kernel there with a pointer into this one's memory
+        int sdev = -1;
+        cudaError_t e = cudaStreamGetDevice(st, &sdev);
+        if (e != cudaSuccess) return fail(ADV_ERR_CUDA, "cudaStreamGetDevice: %s", cudaGetErrorString(e));
+        if (sdev != dev)
+            return fail(ADV_ERR_INVALID, "the stream belongs to device %d but device %d is current: call cudaSetDevice(%d) "
+                                         "before every call of adv_burgers3d_stage_f64_noalloc", sdev, dev, sdev);
+    }
+    double* scratch = noalloc_rowacc_for_device(dev, &rc);
+    if (!scratch) return rc;
     if (a->stage == 1 && a->k_begin >= 0 && a->k_end <= a->nzs && a->k_begin < a->k_end) {
         // the accumulator of a new time step starts from zero (the reference zeroes Lu once per step,
         // main.c:202); whatever an earlier call left in the shared array must not leak into this one.

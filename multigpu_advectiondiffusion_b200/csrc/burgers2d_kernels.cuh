@@ -21,6 +21,38 @@
 
 namespace adv {
 
+// Parity anchor (ADV_BURGERS_DIRECT=1), the 2-D twin of burgers3d_stage_direct: one thread per cell, every
+// thread evaluates its own four faces with the reference's operand order and IEEE divisions
+// (Reconstruct1d, Kernels.cu:103-212; `Lu = -(fu-fu_old)/dx`, `Lu -= (fu-fu_old)/dy`, :273,:345).  Slow on
+// purpose; it separates "different rounding" from "different result" when the tile kernel is questioned.
+template <typename REAL, int W, bool PEER>
+__global__ void __launch_bounds__(256)
+burgers2d_stage_direct(BurgersArgs<REAL> a, const REAL* __restrict__ u, const REAL* __restrict__ uo, REAL* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = a.kb + blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= a.nx || j >= a.ke) return;
+    const long long P = a.pitch, o = (long long)i + P * j;
+    const REAL q = u[o];
+    REAL Lu = REAL(0);
+    if (j >= a.own_lo && j < a.own_hi) {
+        if (i >= 2 && i <= a.nx - 4) {          // x sweep: cells 2..nx-4, flux at 2-1/2 taken as 0 (Kernels.cu:249,273)
+            const REAL fp = face_flux_ref<REAL, W>(u[o - 2], u[o - 1], q, u[o + 1], u[o + 2], u[o + 3]);
+            const REAL fm = (i == 2) ? REAL(0) : face_flux_ref<REAL, W>(u[o - 3], u[o - 2], u[o - 1], q, u[o + 1], u[o + 2]);
+            Lu = -(fp - fm) / a.dx;
+        }
+        if (i >= 3 && i <= a.nx - 4) {          // y sweep: columns 3..nx-4, real seed flux (Kernels.cu:311-345)
+            const REAL gp = face_flux_ref<REAL, W>(u[o - 2 * P], u[o - P], q, u[o + P], u[o + 2 * P], u[o + 3 * P]);
+            const REAL gm = face_flux_ref<REAL, W>(u[o - 3 * P], u[o - 2 * P], u[o - P], q, u[o + P], u[o + 2 * P]);
+            Lu -= (gp - gm) / a.dy;
+        }
+    }
+    const REAL qo = (a.stage == 1) ? q : uo[o];
+    const REAL res = rk_combine<REAL>(a.stage, q, qo, Lu, a.dt);
+    out[o] = res;
+    if (PEER) a.out2[a.off2 + o] = res;
+}
+
 template <typename REAL>
 struct Burgers2dSmem {
     static constexpr int TX = 64, TY = 16, H = 3, RP = TX + 2 * H, ROWS = TY + 2 * H;

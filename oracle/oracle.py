@@ -30,6 +30,31 @@ def lib():
     return _LIB
 
 
+_LIB_FMA = None
+
+
+class fma_variant:
+    """Context manager: inside it every routine of this module runs the SAME C restatement compiled with
+    -mfma -ffp-contract=fast (oracle/Makefile, libadvdiff_oracle_fma.so).  That build is not a parity target; the
+    distance between it and the default (contraction off) build is the rounding bracket of a run."""
+
+    def __enter__(self):
+        global _LIB, _LIB_FMA
+        if _LIB_FMA is None:
+            path = os.path.join(_HERE, "libadvdiff_oracle_fma.so")
+            if not os.path.exists(path):
+                build()
+            _LIB_FMA = C.CDLL(path, mode=os.RTLD_LOCAL)
+        self._saved = lib()
+        _LIB = _LIB_FMA
+        return self
+
+    def __exit__(self, *exc):
+        global _LIB
+        _LIB = self._saved
+        return False
+
+
 def _sfx(dtype):
     dtype = np.dtype(dtype)
     if dtype == np.float64:

@@ -195,19 +195,34 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         s.step(nsteps)
         s.sync()
         u = s.download()
+        # and once more WITHOUT any host barrier between the ranks: what comes back from adv_download -- ghost
+        # planes included -- goes straight into adv_upload and is stepped again.  A rank whose stream is idle
+        # must therefore already hold its neighbours' last stage in its ghost planes (halo_quiesce in
+        # csrc/advdiff.cu); stale ghost planes here would break the comparison with the 1-rank run below.
+        s.upload(u)
+        s.step(nsteps)
+        u_again = s.download()
     parts = [None] * P if rank == 0 else None
     dist.gather_object(u, parts, dst=0)
+    parts_again = [None] * P if rank == 0 else None
+    dist.gather_object(u_again, parts_again, dst=0)
     if rank == 0:
-        merged = g.copy()
+        merged, merged_again = g.copy(), g.copy()
         nzl = nz // P
         for r in range(P):
             merged[r * nzl + 3: r * nzl + 3 + nzl] = parts[r][3:3 + nzl]
+            merged_again[r * nzl + 3: r * nzl + 3 + nzl] = parts_again[r][3:3 + nzl]
         with adv.Solver(target, nx, ny, nz_arg, coef=coef, device=0) as s1:
             s1.upload(g)
             s1.step(nsteps)
             one = s1.download()
+            s1.step(nsteps)
+            two = s1.download()
         one[:3], one[-3:] = g[:3], g[-3:]
+        two[:3], two[-3:] = g[:3], g[-3:]
         assert np.array_equal(merged, one), "P=%d differs from P=1 on the GPU: %g" % (P, float(np.abs(merged - one).max()))
+        assert np.array_equal(merged_again, two), "P=%d, download -> upload -> step with no barrier, differs from P=1: %g" % (
+            P, float(np.abs(merged_again - two).max()))
         if target == "burgers2d_mgpu":
             want, _ = orc.burgers2d_mgpu(g, 1e9, CFL=coef, max_steps=nsteps)
         elif target == "heat2d_mgpu":

@@ -30,25 +30,81 @@ def test_oracle_reproduces_the_recorded_iteration_counts():
     assert i["it"] == 101
 
 
-@pytest.mark.gpu
-def test_gpu_runs_of_the_recorded_configurations():
-    """Same four configurations through the C ABI: iteration counts as recorded, fields within 1e-12 of the oracle
-    (the full 400 x 400 x 406 Burgers run is checked for its step count on a thin grid; its oracle would take
-    half an hour on the CPU)."""
+def _gpu(target, u0, tend, **kw):
     import multigpu_advectiondiffusion_b200 as adv
+    return adv.solve_host(target, u0, tend, **kw)
+
+
+@pytest.mark.gpu
+def test_gpu_step_counts_of_the_recorded_configurations():
+    """The time loop alone (a10): the library takes exactly the recorded number of steps.  Kept apart from the
+    field comparisons below so that a tolerance question can never hide a step-count regression."""
+    _, gi = _gpu("burgers3d_mgpu", orc.ic_burgers3d_mgpu(400, 20, 20, 2.0, 2.0, 4.0), 0.40, lx=2.0, ly=2.0, lz=4.0, coef=0.30)
+    assert gi["it"] == 267 and gi["t"] == 0.40
+    _, gi = _gpu("burgers2d_mgpu", orc.ic_burgers2d_mgpu(400, 400), 0.40, coef=0.40)
+    assert gi["it"] == 200 and gi["t"] == 0.40
+    u0 = orc.ic_heat2d_mgpu(400, 400)
+    _, wi = orc.heat2d_mgpu(u0, 1)
+    _, gi = _gpu("heat2d_mgpu", u0, wi["dt"] * 1000, coef=1.0)
+    assert gi["it"] == 1001
+    u0 = orc.ic_heat3d_mgpu(400, 200, 200)
+    _, wi = orc.heat3d(u0, 1, "mgpu", 1.0, 2.0, 2.0, 2.0)
+    _, gi = _gpu("heat3d_mgpu", u0, wi["dt"] * 100, coef=1.0)
+    assert gi["it"] == 101
+
+
+@pytest.mark.gpu
+def test_gpu_recorded_burgers3d_run_vs_oracle():
+    """MultiGPU/Burgers3d_Baseline/Run.m:4-14 on a thin grid with the recorded nx (the full 400 x 400 x 406 oracle
+    run would take half an hour of CPU): 267 steps to t = 0.40, whole padded array within 1e-12.  The rounding
+    bracket of this case stays at 2e-15 to the end (profiles/r02_fma_bracket.json), so the plain bar applies."""
     u0 = orc.ic_burgers3d_mgpu(400, 20, 20, 2.0, 2.0, 4.0)
-    got, gi = adv.solve_host("burgers3d_mgpu", u0, 0.40, lx=2.0, ly=2.0, lz=4.0, coef=0.30)
+    got, gi = _gpu("burgers3d_mgpu", u0, 0.40, lx=2.0, ly=2.0, lz=4.0, coef=0.30)
     want, wi = orc.burgers3d_mgpu(u0, 0.40, 0.30, 2.0, 2.0, 4.0)
-    assert gi["it"] == wi["it"] == 267 and orc.rel_err(got, want) <= 1e-12
+    assert gi["it"] == wi["it"]
+    assert orc.rel_err(got, want) <= 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("direct", [False, True], ids=["tile-kernel", "reference-operand-order-kernel"])
+def test_gpu_recorded_burgers2d_run_vs_oracle(direct, monkeypatch):
+    """MultiGPU/Burgers2d_Baseline/Run.m:4-14 (400 x 406, tEnd 0.40, CFL 0.40, 200 steps), both 2-D kernels.
+
+    Up to t = 0.20 (100 steps, before the Gaussian steepens into a shock) the bar is the plain 1e-12.  At t = 0.40
+    the run is past the shock time and WENO weight switching amplifies last-bit differences: the SAME C source
+    built with and without FMA contraction differs by 1.3e-11 there (tests/test_fma_bracket.py pins that number),
+    so no implementation that rounds differently from gcc -ffp-contract=off -- nvcc fuses a*b+c, and the tile
+    kernel also folds the divisions -- can be held to 1e-12.  Stated tolerance at t = 0.40: 1e-10, i.e. the
+    measured rounding bracket with less than one order of head room.  The reference-operand-order kernel
+    (ADV_BURGERS_DIRECT=1: IEEE divisions, Reconstruct1d's order) lands in the same band, which is what says the
+    tile kernel's distance is rounding and not a defect."""
+    from test_fma_bracket import POST_SHOCK_TOL
+    if direct:
+        monkeypatch.setenv("ADV_BURGERS_DIRECT", "1")
+    else:
+        monkeypatch.delenv("ADV_BURGERS_DIRECT", raising=False)
     u0 = orc.ic_burgers2d_mgpu(400, 400)
-    got, gi = adv.solve_host("burgers2d_mgpu", u0, 0.40, coef=0.40)
+    got, gi = _gpu("burgers2d_mgpu", u0, 0.20, coef=0.40)
+    want, wi = orc.burgers2d_mgpu(u0, 0.20, 0.40)
+    assert gi["it"] == wi["it"] == 100
+    assert orc.rel_err(got, want) <= 1e-12
+    got, gi = _gpu("burgers2d_mgpu", u0, 0.40, coef=0.40)
     want, wi = orc.burgers2d_mgpu(u0, 0.40, 0.40)
-    assert gi["it"] == wi["it"] == 200 and orc.rel_err(got, want) <= 1e-12
+    assert gi["it"] == wi["it"] == 200
+    err = orc.rel_err(got, want)
+    print("burgers2d recorded run, %s: rel err at t=0.40 %.3e" % ("direct" if direct else "tile", err))
+    assert err <= POST_SHOCK_TOL, err
+
+
+@pytest.mark.gpu
+def test_gpu_recorded_heat_runs_vs_oracle():
+    """MultiGPU/Diffusion2d_Baseline/Run.m:4-14 (1001 steps) and MultiGPU/Diffusion3d_Baseline/Run.m:4-14 (101
+    steps): linear problems, no amplification -- 1e-12 over the whole padded array."""
     u0 = orc.ic_heat2d_mgpu(400, 400)
     want, wi = orc.heat2d_mgpu(u0, 1000)
-    got, gi = adv.solve_host("heat2d_mgpu", u0, wi["dt"] * 1000, coef=1.0)
+    got, gi = _gpu("heat2d_mgpu", u0, wi["dt"] * 1000, coef=1.0)
     assert gi["it"] == wi["it"] == 1001 and orc.rel_err(got, want) <= 1e-12
     u0 = orc.ic_heat3d_mgpu(400, 200, 200)
     want, wi = orc.heat3d(u0, 100, "mgpu", 1.0, 2.0, 2.0, 2.0)
-    got, gi = adv.solve_host("heat3d_mgpu", u0, wi["dt"] * 100, coef=1.0)
+    got, gi = _gpu("heat3d_mgpu", u0, wi["dt"] * 100, coef=1.0)
     assert gi["it"] == wi["it"] == 101 and orc.rel_err(got, want) <= 1e-12

@@ -65,6 +65,57 @@ def test_noalloc_matches_the_allocating_entry_point_two_steps_in_a_row():
     assert np.abs(A2.cpu().numpy() - u0).max() > 1e-3
 
 
+@pytest.mark.parametrize("device", [0, 1])
+def test_noalloc_in_plane_windows_matches_the_oracle(device):
+    """Two whole time steps through the allocation-free entry point, each stage cut into three plane windows
+    (as a caller overlapping a halo exchange would), checked against the CPU oracle of the reference program --
+    not only against the sibling entry point.  Stage 1 clears just the rows of the window it produces, so a
+    later window must not wipe what an earlier one accumulated; the j = 2 row feeds back into genuine cells
+    above 1e-12, which is what makes this comparison sensitive to it.  Device 1 (when the box has one) checks
+    that each GPU gets the address of its own copy of the array."""
+    import torch
+    from oracle import oracle as orc
+    if torch.cuda.device_count() <= device:
+        pytest.skip("needs %d GPUs" % (device + 1))
+    nx, ny, nz = 40, 36, 30
+    NZ = nz + 6
+    d = (2.0 / (nx - 1), 2.0 / (ny - 1), 2.0 / (nz - 1))
+    dt = 0.3 * d[0]
+    u0 = orc.ic_burgers3d_mgpu(nx, ny, nz)
+    want, wi = orc.burgers3d_mgpu(u0, 1e9, max_steps=2)
+    assert wi["it"] == 2 and wi["dt"] == dt
+    dev = torch.device("cuda:%d" % device)
+    L = adv.lib()
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        A = torch.from_numpy(u0).to(dev); B = torch.empty_like(A); Cb = torch.empty_like(A)
+        windows = ((0, 9), (9, 20), (20, NZ))
+        for step in range(2):
+            for stage, (src, dst) in enumerate(((A, B), (B, Cb), (Cb, B)), start=1):
+                for kb, ke in windows:
+                    a = _args(stage, nx, ny, NZ, nx, dt, d)
+                    a.k_begin, a.k_end = kb, ke
+                    _lib.check(L.adv_burgers3d_stage_f64_noalloc(C.byref(a), src.data_ptr(), A.data_ptr(), dst.data_ptr(), st))
+            A, B = B, A
+        torch.cuda.synchronize()
+        got = A.cpu().numpy()
+    got[:3], got[-3:] = u0[:3], u0[-3:]         # Merge_domains leaves the pad planes of the output at their IC
+    assert orc.rel_err(got, want) <= TOL64
+
+
+def test_noalloc_refuses_a_stream_of_another_device():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    with torch.cuda.device(1):
+        s1 = torch.cuda.Stream()
+    torch.cuda.set_device(0)
+    u = torch.zeros((2,), dtype=torch.float64, device="cuda:0")
+    a = _args(1, 16, 16, 16, 16, 1e-3, (1e-2, 1e-2, 1e-2))
+    rc = adv.lib().adv_burgers3d_stage_f64_noalloc(C.byref(a), u.data_ptr(), u.data_ptr(), u.data_ptr() + 8, s1.cuda_stream)
+    assert rc == 1 and "current" in adv.lib().adv_last_error().decode()
+
+
 def test_noalloc_refuses_fields_larger_than_its_scratch():
     import torch
     dev = torch.device("cuda:0")
