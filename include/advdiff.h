@@ -132,6 +132,11 @@ int  adv_download(adv_solver* s, void* host_local);
 /* Reference initial condition generated on the host with libm exp exactly as the reference
  * does (Call_Init3D / Init_domain case per target), sliced to this rank and uploaded. */
 int  adv_init_reference_ic(adv_solver* s);
+/* The same closed forms evaluated by a kernel straight into the slab (the reference fills the
+ * whole padded domain serially on every rank, main.c:70-73 + Tools.c:124-176).  The device exp() is not the
+ * host libm's: values agree with adv_init_reference_ic to the last bit or two, not bit for bit, so parity
+ * runs keep the host generator and throughput runs use this one. */
+int  adv_init_reference_ic_device(adv_solver* s);
 
 /* nsteps fixed-dt time steps (heat drivers' `for it < iters`).  Asynchronous. */
 int  adv_step(adv_solver* s, int nsteps);
@@ -167,6 +172,11 @@ int  adv_peer_handle(adv_solver* s, unsigned char handle[64]);
 int  adv_peer_connect(adv_solver* s, const unsigned char* left_handle, const unsigned char* right_handle);
 int  adv_peer_connect_local(adv_solver* s, adv_solver* left, adv_solver* right);
 int  adv_halo_mode(const adv_solver* s);
+/* The exchange of one stage alone, timed on the device (SURVEY 8d "Halo metric"; the reference's exchange is
+ * main.c:208-316): `reps` times, every rank ships its 3 boundary planes per neighbour into the neighbours'
+ * ghost planes (the values already there -- the field is unchanged) and waits for theirs.  Collective: call
+ * on every rank.  ms_per_exchange = CUDA-event time / reps; bytes_sent_per_exchange = 3 planes x neighbours. */
+int  adv_halo_probe(adv_solver* s, int reps, float* ms_per_exchange, double* bytes_sent_per_exchange);
 
 /* One-call convenience used by the drivers: create + upload + run + download + destroy on host
  * buffers (whole padded domain, single rank).  Mirrors one run of a reference binary. */

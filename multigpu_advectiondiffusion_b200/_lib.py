@@ -64,6 +64,8 @@ SIGNATURES = {
     "adv_upload": (C.c_int, [_P, _P]),
     "adv_download": (C.c_int, [_P, _P]),
     "adv_init_reference_ic": (C.c_int, [_P]),
+    "adv_init_reference_ic_device": (C.c_int, [_P]),
+    "adv_halo_probe": (C.c_int, [_P, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
     "adv_step": (C.c_int, [_P, C.c_int]),
     "adv_run_until": (C.c_int, [_P, C.c_double, C.c_int] + [C.POINTER(C.c_double)] * 3),
     "adv_run_until_cfl": (C.c_int, [_P, C.c_double, C.c_int] + [C.POINTER(C.c_double)] * 3),

@@ -463,6 +463,7 @@ struct adv_solver {
     bool peer_is_ipc[2];
     int p2p;                    // 1: halo planes are stored straight into the neighbours' ghost planes
     unsigned stage_counter;     // stages executed so far (the value the halo flags carry)
+    unsigned probe_counter;     // exchanges run by adv_halo_probe (carried by the probe flags)
     // small single-rank problems are launch-bound: three time steps (one full rotation of the three
     // buffers, nine stage launches) are captured once into a CUDA graph and replayed
     cudaGraphExec_t graph_exec;
@@ -781,6 +782,81 @@ extern "C" int adv_init_reference_ic(adv_solver* s)
 }
 
 // ------------------------------------------------------------------------------------------
+// The same initial conditions generated on the device, straight into the slab: at 1024^3 the
+// reference fills the whole padded domain serially on every rank (main.c:70-73, Tools.c:124-176).  For
+// throughput runs only: the device's exp() is not the host libm's, so the values agree with
+// adv_init_reference_ic to the last bit or two, not bit for bit -- parity runs keep the host generator.
+// ------------------------------------------------------------------------------------------
+template <typename REAL>
+__global__ void __launch_bounds__(256)
+reference_ic_kernel(REAL* __restrict__ h, int target, int nx, int ny, int units, long long pitch, int NZ, int kg0,
+                    REAL dx, REAL dy, REAL dz)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= nx) return;
+    for (int kl = blockIdx.z; kl < units; kl += gridDim.z) {
+        const int k = kl + kg0;
+        REAL v = 0;
+        switch (target) {
+        case ADV_TARGET_HEAT2D_SGPU:
+            v = exp(-((-5 + i * dx) * (-5 + i * dx) + (-5 + j * dy) * (-5 + j * dy)) / (4 * 1.0 * 0.1));
+            if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1) v = 0.0;
+            break;
+        case ADV_TARGET_HEAT3D_SGPU_BASELINE:
+        case ADV_TARGET_HEAT3D_SGPU_BLOCKING:
+            v = exp(-((-5 + i * dx) * (-5 + i * dx) + (-5 + j * dy) * (-5 + j * dy) + (-5 + k * dz) * (-5 + k * dz)) / (4 * 1.0 * 0.1));
+            if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1 || k == 0 || k == NZ - 1) v = 0.0;
+            break;
+        case ADV_TARGET_HEAT3D_MGPU:
+            v = (i >= nx / 4 && i < 3 * nx / 4 && j >= ny / 4 && j < 3 * ny / 4 && k >= NZ / 4 && k < 3 * NZ / 4) ? 1. : 0.;
+            break;
+        case ADV_TARGET_BURGERS3D_SGPU: {
+            const REAL x = i * dx, y = j * dy, z = k * dz;
+            v = 1.0 * exp(-((x - 1.0) * (x - 1.0) + (y - 1.0) * (y - 1.0) + (z - 1.0) * (z - 1.0)) / 0.1);
+            break;
+        }
+        case ADV_TARGET_BURGERS3D_MGPU:
+            if (i == 0 || i == nx - 1 || j == 0 || j == ny - 1 || k == 0 || k == NZ - 1) v = 0.0;
+            else v = 1.0 * exp(-(((0.5 * (nx - 1) - i) * dx * (0.5 * (nx - 1) - i) * dx) +
+                                  ((0.5 * (ny - 1) - j) * dy * (0.5 * (ny - 1) - j) * dy) +
+                                  ((0.5 * (NZ - 1) - k) * dz * (0.5 * (NZ - 1) - k) * dz)) / 0.1);
+            break;
+        case ADV_TARGET_HEAT2D_MGPU:        // y-slab: one row per unit, k = global row, ny == 1
+            v = (sqrtf((float)((i * 1. / (nx - 1) - 0.5) * (i * 1. / (nx - 1) - 0.5) +
+                               (k * 1. / (NZ - 1) - 0.5) * (k * 1. / (NZ - 1) - 0.5))) < 0.2) ? 1.0 : 0.0;
+            break;
+        case ADV_TARGET_BURGERS2D_MGPU:
+            if (i == 0 || i == nx - 1 || k == 0 || k == NZ - 1) v = 0.0;
+            else v = 1.0 * exp(-(((0.5 * (nx - 1) - i) * dx * (0.5 * (nx - 1) - i) * dx) +
+                                  ((0.5 * (NZ - 1) - k) * dy * (0.5 * (NZ - 1) - k) * dy)) / 0.1);
+            break;
+        }
+        h[(long long)i + pitch * ((long long)j + (long long)ny * kl)] = v;
+    }
+}
+
+extern "C" int adv_init_reference_ic_device(adv_solver* s)
+{
+    if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    const adv_desc& d = s->d;
+    const int NZ = is_mgpu(d.target) ? s->nsplit + 2 * ADV_RADIUS : d.nz;
+    const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;
+    dim3 block(256, 1, 1), grid((d.nx + 255) / 256, s->urows, s->nzs < 1024 ? s->nzs : 1024);
+    if (s->esz == 8)
+        reference_ic_kernel<double><<<grid, block, 0, s->stream>>>((double*)s->buf[s->cur], d.target, d.nx, s->urows, s->nzs,
+                                                                      (long long)s->pitch, NZ, kg0, s->dx, s->dy, s->dz);
+    else
+        reference_ic_kernel<float><<<grid, block, 0, s->stream>>>((float*)s->buf[s->cur], d.target, d.nx, s->urows, s->nzs,
+                                                                     (long long)s->pitch, NZ, kg0, (float)s->dx, (float)s->dy, (float)s->dz);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->uploaded = true;
+    return ADV_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // one time step = three fused stages over ping-pong buffers A (u^n), B, C:
 //   B = S1(A);  C = S2(B; A);  B = S3(C; A);  then A <-> B.      (no uo copy, no Lu array)
 // With ranks > 1 each stage computes the two 3-plane boundary slabs first, hands them to the
@@ -958,6 +1034,94 @@ static int halo_quiesce(adv_solver* s)
     if (s->d.rank > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, s->stage_counter))) return rc;
     if (s->d.rank < s->d.nranks - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, s->stage_counter))) return rc;
     return ADV_OK;
+}
+
+// ---- the exchange alone, timed (SURVEY 8d "Halo metric") -------------------------------------------
+// What a stage ships -- three boundary planes per neighbour -- and nothing else: per repetition every rank
+// stores its boundary planes into its neighbours' ghost planes (the values already there: the field does not
+// change), the last CTA of each copy raises the neighbour's probe flag, and the rank waits for its own probe
+// flags.  CUDA events around the loop give the time of one complete exchange as this rank sees it, neighbours'
+// sends included.  NCCL mode times HaloComm::exchange the same way.  Probe flags are separate words of the
+// flag block, so the stage counters of the time loop are untouched.
+enum { FLAG_PROBE_FROM_LEFT = 96, FLAG_PROBE_FROM_RIGHT = 112, PROBE_TICKET_LEFT = 80, PROBE_TICKET_RIGHT = 84 };
+
+__global__ void __launch_bounds__(256)
+halo_probe_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n16, unsigned* ticket,
+                       volatile unsigned* peer_flag, unsigned value)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(ticket, 1u);
+        if (t == gridDim.x - 1) {           // last CTA: every other CTA's stores are fenced before its ticket
+            *ticket = 0;
+            __threadfence_system();
+            *peer_flag = value;
+        }
+    }
+}
+
+extern "C" int adv_halo_probe(adv_solver* s, int reps, float* ms_per_exchange, double* bytes_sent_per_exchange)
+{
+    if (!s || !ms_per_exchange) return fail(ADV_ERR_INVALID, "NULL argument");
+    if (s->d.nranks < 2) return fail(ADV_ERR_INVALID, "the halo probe needs nranks > 1");
+    if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_halo_probe before adv_upload");
+    if (reps < 1) reps = 1;
+    CUDA_TRY(cudaSetDevice(s->d.device));
+    const int P = s->d.nranks, r = s->d.rank, R = ADV_RADIUS;
+    const size_t plane_b = s->pitch * (size_t)s->urows * s->esz, bytes = (size_t)R * plane_b;
+    const int nnb = (r > 0 ? 1 : 0) + (r < P - 1 ? 1 : 0);
+    if (bytes_sent_per_exchange) *bytes_sent_per_exchange = (double)bytes * nnb;
+    char* field = (char*)s->buf[s->cur];
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    int rc = ADV_OK;
+    if (!s->p2p) {
+        CUDA_TRY(cudaStreamWaitEvent(s->comm_stream, s->ev_comm, 0));
+        CUDA_TRY(cudaEventRecord(e0, s->comm_stream));
+        for (int n = 0; n < reps && !rc; n++)
+            rc = s->comm.exchange(field, s->pitch * (size_t)s->urows, s->nzs, s->esz, s->comm_stream, g_err, sizeof(g_err));
+        CUDA_TRY(cudaEventRecord(e1, s->comm_stream));
+        CUDA_TRY(cudaEventRecord(s->ev_comm, s->comm_stream));
+    } else {
+        stream_wait32_fn w = get_stream_wait32();
+        unsigned* flags = (unsigned*)(s->arena + s->off_flags);
+        const size_t off_cur = (size_t)(field - s->arena);
+        int dev_sms = 148;
+        cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, s->d.device);
+        CUDA_TRY(cudaEventRecord(e0, s->stream));
+        for (int n = 0; n < reps; n++) {
+            const unsigned c = ++s->probe_counter;
+            if (r > 0)        // my planes [3,6) -> left neighbour's ghost planes [nzs-3, nzs)
+                halo_probe_copy_kernel<<<2 * dev_sms, 256, 0, s->stream>>>(
+                    (const uint4*)(field + (size_t)R * plane_b), (uint4*)(s->peer_base[0] + off_cur + (size_t)(s->nzs - R) * plane_b), bytes / 16,
+                    flags + PROBE_TICKET_LEFT, (volatile unsigned*)(s->peer_base[0] + s->off_flags) + FLAG_PROBE_FROM_RIGHT, c);
+            if (r < P - 1)    // my planes [nzs-6, nzs-3) -> right neighbour's ghost planes [0, 3)
+                halo_probe_copy_kernel<<<2 * dev_sms, 256, 0, s->stream>>>(
+                    (const uint4*)(field + (size_t)(s->nzs - 2 * R) * plane_b), (uint4*)(s->peer_base[1] + off_cur), bytes / 16,
+                    flags + PROBE_TICKET_RIGHT, (volatile unsigned*)(s->peer_base[1] + s->off_flags) + FLAG_PROBE_FROM_LEFT, c);
+            CUDA_TRY(cudaGetLastError());
+            const int which[2] = {FLAG_PROBE_FROM_LEFT, FLAG_PROBE_FROM_RIGHT};
+            for (int side = 0; side < 2; side++) {
+                if ((side == 0 && r == 0) || (side == 1 && r == P - 1)) continue;
+                bool done = false;
+                if (w) done = w((CUstream)s->stream, (CUdeviceptr)(flags + which[side]), c, 0) == CUDA_SUCCESS;
+                if (!done) { halo_wait_kernel<<<1, 1, 0, s->stream>>>(flags + which[side], c); CUDA_TRY(cudaGetLastError()); }
+            }
+        }
+        CUDA_TRY(cudaEventRecord(e1, s->stream));
+    }
+    if (!rc) {
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        *ms_per_exchange = ms / reps;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
 }
 
 static int do_step(adv_solver* s, double dt)

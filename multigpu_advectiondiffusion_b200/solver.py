@@ -93,6 +93,16 @@ class Solver:
     def init_reference_ic(self):
         check(lib().adv_init_reference_ic(self._h))
 
+    def init_reference_ic_device(self):
+        """same closed forms evaluated on the device (throughput runs; last-bit differences from the host libm)"""
+        check(lib().adv_init_reference_ic_device(self._h))
+
+    def halo_probe(self, reps=50):
+        """(ms per exchange, bytes this rank sends per exchange): the 3-plane exchange of one stage, alone"""
+        ms, b = C.c_float(), C.c_double()
+        check(lib().adv_halo_probe(self._h, reps, C.byref(ms), C.byref(b)))
+        return ms.value, b.value
+
     # -- fused NVLink halo exchange (ranks = processes): exchange the 64-byte handles any way you like
     def peer_handle(self):
         h = (C.c_ubyte * 64)()

@@ -34,3 +34,14 @@ int orc_num_threads(void)
     return 1;
 #endif
 }
+
+/* torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; a timed CPU baseline has to ask for the
+ * host's cores explicitly.  n <= 0 leaves the setting alone. */
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}

@@ -52,6 +52,7 @@ ORC_DECL(double, f64)
 ORC_DECL(float, f32)
 
 int orc_num_threads(void);
+void orc_set_num_threads(int n);
 
 #ifdef __cplusplus
 }

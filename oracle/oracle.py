@@ -72,6 +72,17 @@ def num_threads():
     return lib().orc_num_threads()
 
 
+def use_all_cores():
+    """OpenMP thread count := the cores this process may run on (torchrun exports OMP_NUM_THREADS=1).  Both
+    oracle libraries share one libgomp, so this also covers matlab_port.c.  Returns the count in force."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    lib().orc_set_num_threads(int(n))
+    return num_threads()
+
+
 # ---------------------------------------------------------------- ICs
 def ic_heat3d_sgpu(nx, ny, nz, L=10, W=10, H=10, dtype=np.float64):
     s, R = _sfx(dtype)

@@ -25,6 +25,12 @@ def hashes():
     return {k: hashlib.md5("\n".join(v).encode()).hexdigest() for k, v in funcs.items()}
 
 
+def family_hash(hashes_by_kernel, family):
+    """one hash for all instantiations of a kernel template (mangled names containing `family`)"""
+    items = sorted((k, v) for k, v in hashes_by_kernel.items() if family in k)
+    return hashlib.md5(json.dumps(items).encode()).hexdigest() if items else None
+
+
 if __name__ == "__main__":
     new = hashes()
     if len(sys.argv) > 1:
