@@ -16,6 +16,7 @@
 
 #include "burgers_kernels.cuh"
 #include "burgers2d_kernels.cuh"
+#include "burgers_pair_kernels.cuh"
 #include "reduce.cuh"
 #include "common.cuh"
 #include "halo.cuh"
@@ -390,8 +391,42 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     dim3 grid((a->nx + 31) / 32, (a->ny + 3) / 4, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
     const bool force_direct = env_on("ADV_BURGERS_DIRECT");   // A/B switch for tests and profiling
     fill_weno_consts<REAL>(b, mg ? WENO_JS : WENO_Z);
-    if (!force_direct) {
-        // ring kernel: 32x16 tile, 2 cells per thread, 8+1 warps, 2 CTAs/SM
+    // default: the pair kernel (TMA-staged planes; needs 16-byte rows for the tensor map)
+    const bool pair_ok = !force_direct && !env_on("ADV_BURGERS_RING") && get_tmap_encode() != nullptr &&
+                         ((uintptr_t)u_in % 16 == 0) && ((a->pitch * sizeof(REAL)) % 16 == 0) && a->nx >= 8;
+    if (pair_ok) {
+        typedef BurgersPairSmem<REAL> S;
+        CUtensorMap tm;
+        rc = encode_tmap3(&tm, sizeof(REAL), u_in, a->nx, a->ny, a->nzs, a->pitch, S::RP, S::ROWS);
+        if (rc) return rc;
+        const int planes = a->k_end - a->k_begin;
+        const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + S::TY - 1) / S::TY;
+        int sms = 148;
+        { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        const int target = env_int("ADV_BURGERS_WAVES", 6) * 2 * sms;      // ~6 waves of 2 CTAs per SM ...
+        int nch = (target + gx * gy - 1) / (gx * gy);
+        const int minchunk = env_int("ADV_BURGERS_MINCHUNK", 16);           // ... but chunks of >= 16 planes (5 planes of z run-in each)
+        if (nch > planes / minchunk) nch = planes / minchunk;
+        if (nch < 1) nch = 1;
+        const int chunk = (planes + nch - 1) / nch;
+        dim3 pgrid(gx, gy, (planes + chunk - 1) / chunk), pblock(32, S::NW, 1);
+        const REAL* uo_ = a->stage == 1 ? u_in : uo;
+        const size_t shm = sizeof(S);
+#define LAUNCH_PAIR(W_, M_, STAGE_, PEER_) do { \
+            auto kfn = burgers3d_stage_pair<REAL, W_, M_, STAGE_, PEER_>; \
+            CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
+            kfn<<<pgrid, pblock, shm, st>>>(tm, b, chunk, u_in, uo_, u_out, rowacc); } while (0)
+#define LAUNCH_PAIR_S(W_, M_, PEER_) do { \
+            if (a->stage == 1) LAUNCH_PAIR(W_, M_, 1, PEER_); \
+            else if (a->stage == 2) LAUNCH_PAIR(W_, M_, 2, PEER_); \
+            else LAUNCH_PAIR(W_, M_, 3, PEER_); } while (0)
+        if (!mg) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, false);
+        else if (b.out2) LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, true);
+        else LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, false);
+#undef LAUNCH_PAIR_S
+#undef LAUNCH_PAIR
+    } else if (!force_direct) {
+        // ring kernel (ADV_BURGERS_RING=1, or rows that are not 16-byte aligned): 32x16 tile, 2 cells per thread, 8+1 warps, 2 CTAs/SM
         constexpr int TY = 16, CPT = 2, MINB = 2;
         const int planes = a->k_end - a->k_begin;
         const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
@@ -1095,11 +1130,11 @@ extern "C" int adv_halo_probe(adv_solver* s, int reps, float* ms_per_exchange, d
         for (int n = 0; n < reps; n++) {
             const unsigned c = ++s->probe_counter;
             if (r > 0)        // my planes [3,6) -> left neighbour's ghost planes [nzs-3, nzs)
-                halo_probe_copy_kernel<<<2 * dev_sms, 256, 0, s->stream>>>(
+                halo_probe_copy_kernel<<<8 * dev_sms, 256, 0, s->stream>>>(
                     (const uint4*)(field + (size_t)R * plane_b), (uint4*)(s->peer_base[0] + off_cur + (size_t)(s->nzs - R) * plane_b), bytes / 16,
                     flags + PROBE_TICKET_LEFT, (volatile unsigned*)(s->peer_base[0] + s->off_flags) + FLAG_PROBE_FROM_RIGHT, c);
             if (r < P - 1)    // my planes [nzs-6, nzs-3) -> right neighbour's ghost planes [0, 3)
-                halo_probe_copy_kernel<<<2 * dev_sms, 256, 0, s->stream>>>(
+                halo_probe_copy_kernel<<<8 * dev_sms, 256, 0, s->stream>>>(
                     (const uint4*)(field + (size_t)(s->nzs - 2 * R) * plane_b), (uint4*)(s->peer_base[1] + off_cur), bytes / 16,
                     flags + PROBE_TICKET_RIGHT, (volatile unsigned*)(s->peer_base[1] + s->off_flags) + FLAG_PROBE_FROM_LEFT, c);
             CUDA_TRY(cudaGetLastError());
