@@ -28,8 +28,61 @@
 #pragma once
 #include "burgers_kernels.cuh"
 #include "heat_kernels.cuh"     // tma_load_3d, mbar_expect_tx, mbar_wait_parity
+#include <type_traits>
 
 namespace adv {
+
+// reciprocal from the hardware seed (rcp.approx.ftz.f64, ~2^-23) and ONE cubic correction step:
+// y = y0 (1 + e + e^2), e = 1 - den*y0  ->  relative error e^3 plus rounding; three FMAs instead of the four of two
+// Newton steps
+__device__ __forceinline__ double fast_rcp3(double den)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(den));
+    const double e = fma(-den, y, 1.0);
+    const double r = fma(e, e, e);
+    return fma(y, r, y);
+}
+__device__ __forceinline__ float fast_rcp3(float den) { return __frcp_rn(den); }
+
+// SIX TIMES the one-sided WENO5 value centred on c, from the FORWARD differences along the line
+//   g0 = b-a, g1 = c-b, g2 = d-c, g3 = e-d   and   t_k = g_{k+1} - g_k   of the five values (a, b, c, d, e).
+// REV = false: the value weno_side6(a, b, c, d, e) stands for; REV = true: weno_side6(e, d, c, b, a) -- the same
+// differences read backwards (signs folded into the FMAs), so a cell's minus- and plus-side halves and the halves
+// of the next cell along the line share their differences.  Same formulas as weno_side6, 40 FP64 instructions
+// instead of 43: differences of differences (14 -> 13), the halved P_0 (see BurgersArgs::wp), one cubic
+// reciprocal step.  `we` = BurgersArgs::wp (JS) or ::wc (Z).
+template <typename REAL, int W, bool REV>
+__device__ __forceinline__ REAL weno_core6(REAL c, REAL g0, REAL g1, REAL g2, REAL g3, REAL t0, REAL t1, REAL t2,
+                                           const REAL* __restrict__ we, const REAL* __restrict__ wc)
+{
+    const REAL T0 = REV ? t2 : t0, T2 = REV ? t0 : t2;
+    const REAL sa = fma(REAL(2), g1, t0);       // a - 4b + 3c
+    const REAL sb = fma(REAL(-2), g2, t2);      // 3c - 4d + e
+    const REAL S0 = REV ? sb : sa, S2 = REV ? sa : sb;
+    const REAL S1 = g1 + g2;                    // d - b (enters squared)
+    const REAL q6 = REV ? fma(REAL(6), c, -fma(REAL(2), g1, g2)) : fma(REAL(6), c, fma(REAL(2), g2, g1));
+    (void)g0; (void)g3;
+    const REAL E0 = (we[0] * T0) * T0 + ((we[3] * S0) * S0 + we[6]);
+    const REAL E1 = (we[1] * t1) * t1 + ((we[4] * S1) * S1 + we[7]);
+    const REAL E2 = (we[2] * T2) * T2 + ((we[5] * S2) * S2 + we[8]);
+    const REAL d01 = T0 - t1, d12 = t1 - T2;
+    if (W == WENO_JS) {
+        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;      // P0 is half its textbook value
+        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
+        const REAL num = fma(d12, n2, d01 * n0);
+        const REAL den = fma(REAL(0.5), n0, n1 + n2);
+        return fma(num, fast_rcp3(den), q6);
+    } else {
+        const REAL tau = fabs(E0 - E2);
+        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
+        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
+        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
+        const REAL A = d01 * A0;
+        const REAL num = fma(d12, A2, A + A);
+        return fma(num, fast_rcp3((A0 + A1) + A2), q6);
+    }
+}
 
 template <typename REAL>
 struct BurgersPairSmem {
@@ -47,7 +100,7 @@ struct BurgersPairSmem {
     Slot slot[NSLOT];
     Raw raw[2];
     Exch ex;
-    REAL edge_hn_x[2][TY], edge_hp_x[2][TY];    // hn of column -1, hp of column TX
+    alignas(16) REAL edge_hn_x[2][TY], edge_hp_x[2][TY];    // hn of column -1, hp of column TX (rows 2t, 2t+1 read as one pair)
     unsigned long long bar, full[2], pro;
     static_assert(sizeof(Exch) >= RAWB, "the exchange block doubles as a landing zone of the run-in planes");
     // landing zones of the chunk's five run-in planes: raw[0], raw[1], ex, and slot[5] (one or two boxes)
@@ -119,6 +172,16 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         if (hidx[1] >= 0) sp[hidx[1]] = split(v1);
     };
     auto slot_of = [&](int s0, int d) -> int { int t = s0 + d; return t >= NSLOT ? t - NSLOT : t; };
+    const REAL* __restrict__ we = (W == WENO_JS) ? a.wp : a.wc;
+    // the two halves centred on c along a line (m2, m1, c, p1, p2): hn from the f+ components, hp from the f- ones
+    auto half_n = [&](REAL m2, REAL m1, REAL c, REAL p1, REAL p2) -> REAL {
+        const REAL g0 = m1 - m2, g1 = c - m1, g2 = p1 - c, g3 = p2 - p1;
+        return weno_core6<REAL, W, false>(c, g0, g1, g2, g3, g1 - g0, g2 - g1, g3 - g2, we, wc);
+    };
+    auto half_p = [&](REAL m2, REAL m1, REAL c, REAL p1, REAL p2) -> REAL {
+        const REAL g0 = m1 - m2, g1 = c - m1, g2 = p1 - c, g3 = p2 - p1;
+        return weno_core6<REAL, W, true>(c, g0, g1, g2, g3, g1 - g0, g2 - g1, g3 - g2, we, wc);
+    };
 
     // ---- run-in: planes kb-3 .. kb+1 into slots 0 .. 4, all boxes of a round in flight on one barrier
     {
@@ -138,9 +201,9 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
             __syncthreads();
         }
     }
-    if (tid == 0) {     // plane kb+2: staged by the first iteration
-        mbar_expect_tx(full0 + 8 * ((kb + 2) & 1), (unsigned)S::BOXB);
-        tma_load_3d((unsigned)__cvta_generic_to_shared(sm.raw[(kb + 2) & 1].b), &tmap, i0 - HXR, j0 - H, kb + 2, full0 + 8 * ((kb + 2) & 1));
+    if (tid == 0) {     // plane kb+2: split by the first iteration (n = 0) out of raw[1]
+        mbar_expect_tx(full0 + 8, (unsigned)S::BOXB);
+        tma_load_3d((unsigned)__cvta_generic_to_shared(sm.raw[1].b), &tmap, i0 - HXR, j0 - H, kb + 2, full0 + 8);
     }
 
     // ---- per-cell bookkeeping of rim tiles: which directional contributions a cell takes
@@ -176,26 +239,39 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     const int zlo = max(kb, a.own_lo) - 1, zhi = min(ke, a.own_hi);
 
     // carried from the iteration that computed the pairs of plane p-1
-    REAL X1[2] = {REAL(0), REAL(0)}, X2[2] = {REAL(0), REAL(0)};    // x partial sums of the faces right / left of the cell
+    REAL X1[2] = {REAL(0), REAL(0)}, X2[2] = {REAL(0), REAL(0)};    // 6 x the x face fluxes right / left of the cell
     REAL hpLow = REAL(0), Yint = REAL(0), hnUp = REAL(0);           // own y halves: hp_y(L), hn_y(L)+hp_y(U), hn_y(U)
     REAL hn_prev[2] = {REAL(0), REAL(0)}, Fz_prev[2] = {REAL(0), REAL(0)};
 
     mbar_arrive(bar);
-    unsigned parity = 0, fpar = 0;
+    unsigned fpar = 0;
     int sc = 2;                                          // ring slot of plane p (slot of plane q = (q - (kb-3)) mod 6)
+    // running element offset of cell L in the plane being finished (plane p-1), bumped once per iteration
+    long long om = col0 + Z * (kb - 3);
 
-    auto iteration = [&](auto rim_tag, int p) {
+    // One iteration: centre plane p = kb-1+n.  Buffers that alternate from plane to plane are indexed by the
+    // parity of n (NPAR: compile-time 0/1 in the unrolled steady-state loop, 2 = take it from n).
+    //   ex[n&1], edge_x[n&1]      halves of plane p that cross threads (written in iteration n / n-1, read in n+1 / n)
+    //   raw[(n+1)&1]              box of plane p+3 (issued in iteration n-1, split in iteration n)
+    // STEADY: every plane-level test is known to be true (plane p-1 is finished and owned, planes p and p+1 are
+    // owned and inside the chunk, planes p+3 and p+4 are still to be staged) and is compiled out.
+    auto iteration = [&](auto rim_tag, auto steady_tag, auto par_tag, int p, int n) {
         constexpr bool RIM = decltype(rim_tag)::value;
+        constexpr bool STEADY = decltype(steady_tag)::value;
+        constexpr int NPAR = decltype(par_tag)::value;
+        const int nb = (NPAR == 2) ? (n & 1) : NPAR, eb = nb ^ 1;
         const int m = p - 1;                                                    // the plane this iteration finishes
-        const bool fin = m >= kb;
-        const bool own_m = fin && (m >= a.own_lo && m < a.own_hi);
-        const bool do_z = (p >= zlo && p <= zhi);
-        const bool do_xy = (p < ke) && (p >= a.own_lo && p < a.own_hi);
-        const int eb = m & 1, nb = eb ^ 1;
+        const bool fin = STEADY || m >= kb;
+        const bool own_m = STEADY || (fin && (m >= a.own_lo && m < a.own_hi));
+        const bool do_z = STEADY || (p >= zlo && p <= zhi);
+        const bool do_xy = STEADY || ((p < ke) && (p >= a.own_lo && p < a.own_hi));
+        const bool do_xrim = STEADY || ((p + 1 < ke) && (p + 1 >= a.own_lo && p + 1 < a.own_hi));
+        const bool do_stage = STEADY || (p + 3 <= ke + 2);
+        const bool do_issue = STEADY || (p + 4 <= ke + 2);
+        om += Z;
 
         // (A) u and uo of the plane being finished (L2 hits: the boxes brought them in three planes ago)
         REAL u_m[2] = {REAL(0), REAL(0)}, uo_m[2] = {REAL(0), REAL(0)};
-        const long long om = col0 + Z * m;
         if (fin) {
 #pragma unroll
             for (int c = 0; c < 2; c++)
@@ -206,28 +282,29 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         }
 
         // (B) z halves of plane p from the thread's own ring column (staged by this thread: nothing to wait for)
+        const V2* __restrict__ s = sm.slot[sc].v;
+        const V2 cL = s[ownL], cU = s[ownU];
         REAL Fz[2] = {REAL(0), REAL(0)};
         if (do_z) {
-            const V2 *q0 = sm.slot[slot_of(sc, 4)].v, *q1 = sm.slot[slot_of(sc, 5)].v, *q2 = sm.slot[sc].v,
+            const V2 *q0 = sm.slot[slot_of(sc, 4)].v, *q1 = sm.slot[slot_of(sc, 5)].v,
                      *q3 = sm.slot[slot_of(sc, 1)].v, *q4 = sm.slot[slot_of(sc, 2)].v;
 #pragma unroll
             for (int c = 0; c < 2; c++) {
                 const int own = ownL + c * RP;
-                const V2 v0 = q0[own], v1 = q1[own], v2 = q2[own], v3 = q3[own], v4 = q4[own];
-                const REAL hn = weno_side6<REAL, W>(v0.x, v1.x, v2.x, v3.x, v4.x, wc);
-                const REAL hp = weno_side6<REAL, W>(v4.y, v3.y, v2.y, v1.y, v0.y, wc);
-                Fz[c] = hn_prev[c] + hp;                 // face p-1/2
+                const V2 v0 = q0[own], v1 = q1[own], v2 = c ? cU : cL, v3 = q3[own], v4 = q4[own];
+                const REAL hn = half_n(v0.x, v1.x, v2.x, v3.x, v4.x);
+                const REAL hp = half_p(v0.y, v1.y, v2.y, v3.y, v4.y);
+                Fz[c] = hn_prev[c] + hp;                 // 6 x the face flux at p-1/2
                 hn_prev[c] = hn;
             }
         }
 
-        mbar_wait_hint(bar, parity);
-        parity ^= 1u;
+        mbar_wait_hint(bar, (unsigned)eb);               // phase n-1 (the arrive before the loop is phase -1)
         // everybody is done with the raw buffer of plane p+2: the box of plane p+4 may land there
-        if (tid == 0 && p + 4 <= ke + 2) {
-            const unsigned fb = full0 + 8 * ((p + 4) & 1);
+        if (tid == 0 && do_issue) {
+            const unsigned fb = full0 + 8 * nb;
             mbar_expect_tx(fb, (unsigned)S::BOXB);
-            tma_load_3d((unsigned)__cvta_generic_to_shared(sm.raw[(p + 4) & 1].b), &tmap, i0 - HXR, j0 - H, p + 4, fb);
+            tma_load_3d((unsigned)__cvta_generic_to_shared(sm.raw[nb].b), &tmap, i0 - HXR, j0 - H, p + 4, fb);
         }
 
         // (E) finish plane m: divergence from the carried own halves + the neighbours' halves, RK combine, store
@@ -239,8 +316,8 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
                 REAL Lu = REAL(0);
                 REAL fu = REAL(0), fu_old = REAL(0), gu = REAL(0), gu_old = REAL(0);
                 if (own_m) {
-                    fu = (tx == 31) ? X1[c] + sm.edge_hp_x[eb][r] : X1[c];
-                    fu_old = (tx == 0) ? sm.edge_hn_x[eb][r] + X2[c] : X2[c];
+                    fu = X1[c];
+                    fu_old = X2[c];
                     if (c == 0) { gu = Yint; gu_old = sm.ex.hnU[eb][ty][tx] + hpLow; }
                     else        { gu = hnUp + sm.ex.hpL[eb][ty + 1][tx]; gu_old = Yint; }
                 }
@@ -297,62 +374,87 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
 
         // (F) x and y halves of plane p, centred on the two own cells
         if (do_xy) {
-            const V2* __restrict__ s = sm.slot[sc].v;
-            const V2 cL = s[ownL], cU = s[ownU];
             {
                 const V2 ya_ = s[ownL - 2 * RP], yb = s[ownL - RP], ye = s[ownU + RP], yf = s[ownU + 2 * RP];
-                const REAL hnL_ = weno_side6<REAL, W>(ya_.x, yb.x, cL.x, cU.x, ye.x, wc);
-                const REAL hpL_ = weno_side6<REAL, W>(ye.y, cU.y, cL.y, yb.y, ya_.y, wc);
-                const REAL hnU_ = weno_side6<REAL, W>(yb.x, cL.x, cU.x, ye.x, yf.x, wc);
-                const REAL hpU_ = weno_side6<REAL, W>(yf.y, ye.y, cU.y, cL.y, yb.y, wc);
+                // six rows, two cells: the five forward differences and four second differences per component are shared
+                const REAL G0 = yb.x - ya_.x, G1 = cL.x - yb.x, G2 = cU.x - cL.x, G3 = ye.x - cU.x, G4 = yf.x - ye.x;
+                const REAL T0 = G1 - G0, T1 = G2 - G1, T2 = G3 - G2, T3 = G4 - G3;
+                const REAL hnL_ = weno_core6<REAL, W, false>(cL.x, G0, G1, G2, G3, T0, T1, T2, we, wc);
+                const REAL hnU_ = weno_core6<REAL, W, false>(cU.x, G1, G2, G3, G4, T1, T2, T3, we, wc);
+                const REAL H0 = yb.y - ya_.y, H1 = cL.y - yb.y, H2 = cU.y - cL.y, H3 = ye.y - cU.y, H4 = yf.y - ye.y;
+                const REAL S0 = H1 - H0, S1 = H2 - H1, S2 = H3 - H2, S3 = H4 - H3;
+                const REAL hpL_ = weno_core6<REAL, W, true>(cL.y, H0, H1, H2, H3, S0, S1, S2, we, wc);
+                const REAL hpU_ = weno_core6<REAL, W, true>(cU.y, H1, H2, H3, H4, S1, S2, S3, we, wc);
                 sm.ex.hnU[nb][ty + 1][tx] = hnU_;
                 sm.ex.hpL[nb][ty][tx] = hpL_;
                 hpLow = hpL_; Yint = hnL_ + hpU_; hnUp = hnU_;
             }
+            // the halves beyond the tile's x rim were computed one iteration ago: lanes 0 and 31 take them in
+            // place of the shuffled neighbour half, so the face sums are complete here and the finalisation
+            // has no special lanes
+            const V2 eN = *reinterpret_cast<const V2*>(&sm.edge_hn_x[nb][2 * ty]);
+            const V2 eP = *reinterpret_cast<const V2*>(&sm.edge_hp_x[nb][2 * ty]);
 #pragma unroll
             for (int c = 0; c < 2; c++) {
                 const int own = ownL + c * RP;
                 const V2 cc = c ? cU : cL;
                 const V2 xm2 = s[own - 2], xm1 = s[own - 1], xp1 = s[own + 1], xp2 = s[own + 2];
-                const REAL hn_x = weno_side6<REAL, W>(xm2.x, xm1.x, cc.x, xp1.x, xp2.x, wc);
-                const REAL hp_x = weno_side6<REAL, W>(xp2.y, xp1.y, cc.y, xm1.y, xm2.y, wc);
-                const REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
-                const REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
-                X1[c] = (tx == 31) ? hn_x : hn_x + hpR;
-                X2[c] = (tx == 0) ? hp_x : hnL + hp_x;
+                const REAL hn_x = half_n(xm2.x, xm1.x, cc.x, xp1.x, xp2.x);
+                const REAL hp_x = half_p(xm2.y, xm1.y, cc.y, xp1.y, xp2.y);
+                REAL hpR = __shfl_down_sync(0xffffffffu, hp_x, 1);
+                REAL hnL = __shfl_up_sync(0xffffffffu, hn_x, 1);
+                hpR = (tx == 31) ? (c ? eP.y : eP.x) : hpR;
+                hnL = (tx == 0) ? (c ? eN.y : eN.x) : hnL;
+                X1[c] = hn_x + hpR;
+                X2[c] = hnL + hp_x;
             }
-            // (G) the halves on the tile rim: three warp-rounds, taken in rotation
-            const int role = (ty + p) & 7;
-            if (role < 3) {
+        }
+        // (G) the halves on the tile rim: three warp-rounds, taken in rotation -- y rim of plane p, x rim of plane p+1
+        {
+            const int role = (ty + n) & 7;
+            if ((role < 2 && do_xy) || (role == 2 && do_xrim)) {
                 int oc, st;
                 bool minus;
                 if (role == 0)      { oc = (H - 1) * RP + tx + HXR;  st = RP; minus = true;  }              // hn_y of the row below
                 else if (role == 1) { oc = (H + TY) * RP + tx + HXR; st = RP; minus = false; }              // hp_y of the row above
                 else if (tx < TY)   { oc = (tx + H) * RP + HXR - 1;  st = 1;  minus = true;  }              // hn_x of column -1
                 else                { oc = (tx - TY + H) * RP + HXR + TX; st = 1; minus = false; }          // hp_x of column TX
-                const V2 m2 = s[oc - 2 * st], m1 = s[oc - st], cc = s[oc], p1 = s[oc + st], p2 = s[oc + 2 * st];
-                const REAL v = weno_side6<REAL, W>(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
-                                                    minus ? p1.x : m1.y, minus ? p2.x : m2.y, wc);
+                const V2* __restrict__ sr = (role == 2) ? sm.slot[slot_of(sc, 1)].v : s;
+                const V2 m2 = sr[oc - 2 * st], m1 = sr[oc - st], cc = sr[oc], p1 = sr[oc + st], p2 = sr[oc + 2 * st];
+                const REAL v = half_n(minus ? m2.x : p2.y, minus ? m1.x : p1.y, minus ? cc.x : cc.y,
+                                      minus ? p1.x : m1.y, minus ? p2.x : m2.y);
                 if (role == 0) sm.ex.hnU[nb][0][tx] = v;
                 else if (role == 1) sm.ex.hpL[nb][NW][tx] = v;
-                else if (tx < TY) sm.edge_hn_x[nb][tx] = v;
-                else sm.edge_hp_x[nb][tx - TY] = v;
+                else if (tx < TY) sm.edge_hn_x[eb][tx] = v;
+                else sm.edge_hp_x[eb][tx - TY] = v;
             }
         }
 
         // (C) plane p+3: its box was issued an iteration ago
-        if (p + 3 <= ke + 2) {
-            const int b = (p + 3) & 1;
-            mbar_wait_parity(full0 + 8 * b, (fpar >> b) & 1u);
-            fpar ^= 1u << b;
-            split_plane(sm.raw[b].b, slot_of(sc, 3));
+        if (do_stage) {
+            mbar_wait_parity(full0 + 8 * eb, (fpar >> eb) & 1u);
+            fpar ^= 1u << eb;
+            split_plane(sm.raw[eb].b, slot_of(sc, 3));
         }
         mbar_arrive(bar);
         sc = (sc + 1 == NSLOT) ? 0 : sc + 1;
     };
 
-    if (interior) { for (int p = kb - 1; p <= ke; p++) iteration(BoolTag<false>(), p); }
-    else          { for (int p = kb - 1; p <= ke; p++) iteration(BoolTag<true>(), p); }
+    // steady-state centre planes: see STEADY above
+    const int s_lo = max(kb, a.own_lo) + 1, s_hi = min(min(ke - 2, a.own_hi - 2), a.nzs - 5);
+    auto run = [&](auto rim_tag) {
+        typedef std::integral_constant<int, 0> P0;
+        typedef std::integral_constant<int, 1> P1;
+        typedef std::integral_constant<int, 2> PR;
+        int p = kb - 1, n = 0;
+        for (; p <= ke && (p < s_lo || (n & 1)); p++, n++) iteration(rim_tag, BoolTag<false>(), PR(), p, n);
+        for (; p + 1 <= s_hi; p += 2, n += 2) {
+            iteration(rim_tag, BoolTag<true>(), P0(), p, n);
+            iteration(rim_tag, BoolTag<true>(), P1(), p + 1, n + 1);
+        }
+        for (; p <= ke; p++, n++) iteration(rim_tag, BoolTag<false>(), PR(), p, n);
+    };
+    if (interior) run(BoolTag<false>()); else run(BoolTag<true>());
 }
 
 }  // namespace adv

@@ -63,6 +63,9 @@ struct BurgersArgs {
     // [0..2] r_k*13/12, [3..5] r_k/4, [6..8] r_k*eps with r_k = 1/sqrt(d_k) (JS) or 1 (Z);
     // [9] 2/6 [10] 7/6 [11] 11/6 [12] 1/6 [13] 5/6 [14] 0.75 [15] 0.25 [16..18] d_k = .1 .6 .3 [19] 1/3
     REAL wc[20];
+    // the pair kernel's copy of [0..8] with the k = 0 entries divided by sqrt(2) (JS): P_0 arrives halved, which
+    // turns 2*d01*n0 + d12*n2 over n0+n1+n2 into d01*n0 + d12*n2' over n0/2 + n1' + n2' (one addition less)
+    REAL wp[9];
 };
 
 template <typename REAL>
@@ -79,6 +82,13 @@ inline void fill_weno_consts(BurgersArgs<REAL>& b, int weno)
     b.wc[9] = (REAL)(2.0 / 6); b.wc[10] = (REAL)(7.0 / 6); b.wc[11] = (REAL)(11.0 / 6);
     b.wc[12] = (REAL)(1.0 / 6); b.wc[13] = (REAL)(5.0 / 6); b.wc[14] = (REAL)0.75; b.wc[15] = (REAL)0.25;
     b.wc[19] = (REAL)(1.0 / 3.0);
+    for (int k = 0; k < 3; k++) {
+        const double r = weno == WENO_JS ? 1.0 / sqrt(d[k]) : 1.0;
+        const double h = (weno == WENO_JS && k == 0) ? 1.0 / sqrt(2.0) : 1.0;
+        b.wp[k] = (REAL)(h * r * 13.0 / 12.0);
+        b.wp[3 + k] = (REAL)(h * r * 0.25);
+        b.wp[6 + k] = (REAL)(h * r * 1e-6);
+    }
 }
 
 }  // namespace adv
