@@ -264,7 +264,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         const bool fin = STEADY || m >= kb;
         const bool own_m = STEADY || (fin && (m >= a.own_lo && m < a.own_hi));
         const bool do_z = STEADY || (p >= zlo && p <= zhi);
-        const bool do_xy = STEADY || ((p < ke) && (p >= a.own_lo && p < a.own_hi));
+        const bool do_xy = STEADY || ((p >= kb) && (p < ke) && (p >= a.own_lo && p < a.own_hi));
         const bool do_xrim = STEADY || ((p + 1 < ke) && (p + 1 >= a.own_lo && p + 1 < a.own_hi));
         const bool do_stage = STEADY || (p + 3 <= ke + 2);
         const bool do_issue = STEADY || (p + 4 <= ke + 2);
@@ -299,7 +299,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
             }
         }
 
-        mbar_wait_hint(bar, (unsigned)eb);               // phase n-1 (the arrive before the loop is phase -1)
+        mbar_wait_hint(bar, (unsigned)nb);               // phase n: completed by the arrivals that end iteration n-1 (n = 0: by the arrivals before the loop)
         // everybody is done with the raw buffer of plane p+2: the box of plane p+4 may land there
         if (tid == 0 && do_issue) {
             const unsigned fb = full0 + 8 * nb;
