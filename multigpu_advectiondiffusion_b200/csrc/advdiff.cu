@@ -403,11 +403,19 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + S::TY - 1) / S::TY;
         int sms = 148;
         { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        const int target = env_int("ADV_BURGERS_WAVES", 6) * 2 * sms;      // ~6 waves of 2 CTAs per SM ...
-        int nch = (target + gx * gy - 1) / (gx * gy);
-        const int minchunk = env_int("ADV_BURGERS_MINCHUNK", 16);           // ... but chunks of >= 16 planes (5 planes of z run-in each)
-        if (nch > planes / minchunk) nch = planes / minchunk;
-        if (nch < 1) nch = 1;
+        // z chunks: all CTAs take the same time, so the launch runs in waves of 2 CTAs per SM and costs
+        // waves x (chunk + run-in).  Pick the chunk count that minimises that (chunks of >= 12 planes: 5 planes of
+        // staging and one plane of z halves are the run-in, about 3 planes' worth of work).
+        const int minchunk = env_int("ADV_BURGERS_MINCHUNK", 12), forced = env_int("ADV_BURGERS_NCH", 0);
+        int nch = 1;
+        long long best = -1;
+        for (int c = 1; c <= planes / minchunk || c == 1; c++) {
+            const int ch = (planes + c - 1) / c, nz = (planes + ch - 1) / ch;
+            const long long ctas = (long long)gx * gy * nz, waves = (ctas + 2 * sms - 1) / (2 * sms);
+            const long long cost = waves * (ch + 3);
+            if (best < 0 || cost < best) { best = cost; nch = c; }
+        }
+        if (forced > 0) nch = forced;
         const int chunk = (planes + nch - 1) / nch;
         dim3 pgrid(gx, gy, (planes + chunk - 1) / chunk), pblock(32, S::NW, 1);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;

@@ -132,7 +132,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     const bool interior = (i0 >= 3) && (i0 + TX - 1 <= a.nx - 4) && (j0 >= 3) && (j0 + TY - 1 <= a.ny - 4);
 
     if (tid == 0) {
-        mbar_init(bar, 256);
+        mbar_init(bar, NW);              // one arrival per warp: lane 0, after __syncwarp()
         mbar_init(pro, 1);
         mbar_init(full0, 1);
         mbar_init(full0 + 8, 1);
@@ -243,7 +243,10 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     REAL hpLow = REAL(0), Yint = REAL(0), hnUp = REAL(0);           // own y halves: hp_y(L), hn_y(L)+hp_y(U), hn_y(U)
     REAL hn_prev[2] = {REAL(0), REAL(0)}, Fz_prev[2] = {REAL(0), REAL(0)};
 
-    mbar_arrive(bar);
+    // plane barrier: a warp arrives once (lane 0, after __syncwarp() has ordered the other lanes' shared-memory
+    // writes before it) -- 8 arrivals per phase instead of 256 wake the waiting warps far less often
+    auto warp_arrive = [&]() { __syncwarp(); if (tx == 0) mbar_arrive(bar); };
+    warp_arrive();
     unsigned fpar = 0;
     int sc = 2;                                          // ring slot of plane p (slot of plane q = (q - (kb-3)) mod 6)
     // running element offset of cell L in the plane being finished (plane p-1), bumped once per iteration
@@ -436,7 +439,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
             fpar ^= 1u << eb;
             split_plane(sm.raw[eb].b, slot_of(sc, 3));
         }
-        mbar_arrive(bar);
+        warp_arrive();
         sc = (sc + 1 == NSLOT) ? 0 : sc + 1;
     };
 
