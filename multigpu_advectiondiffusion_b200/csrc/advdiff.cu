@@ -82,8 +82,8 @@ static bool is_2d_mgpu(int t) { return t == ADV_TARGET_HEAT2D_MGPU || t == ADV_T
 static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU || is_2d_mgpu(t); }
 
 // second destination of a stage launch (fused halo exchange); internal, not part of the public stage ABI
-struct PeerOut { void* out2; long long off2; };
-static const PeerOut kNoPeer = {nullptr, 0};
+struct PeerOut { void* out2; long long off2; const double* cfl_dt; const int* cfl_done; unsigned long long* cfl_umax; };
+static const PeerOut kNoPeer = {nullptr, 0, nullptr, nullptr, nullptr};
 
 static int check_stage_args(const adv_stage_args* a, const void* u_in, const void* uo, const void* u_out, int min_n)
 {
@@ -373,6 +373,8 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     if (mg && !rowacc) return fail(ADV_ERR_INVALID, "rowacc scratch is required for ADV_TARGET_BURGERS3D_MGPU");
 
     BurgersArgs<REAL> b;
+    memset(&b, 0, sizeof(b));
+    b.cfl_dt = peer.cfl_dt; b.cfl_done = peer.cfl_done; b.cfl_umax = peer.cfl_umax;
     b.nx = a->nx; b.ny = a->ny; b.nzs = a->nzs;
     b.pitch = (long long)a->pitch; b.plane = (long long)a->pitch * a->ny;
     b.kb = a->k_begin; b.ke = a->k_end; b.own_lo = a->own_lo; b.own_hi = a->own_hi;
@@ -394,6 +396,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     // default: the pair kernel (TMA-staged planes; needs 16-byte rows for the tensor map)
     const bool pair_ok = !force_direct && !env_on("ADV_BURGERS_RING") && get_tmap_encode() != nullptr &&
                          ((uintptr_t)u_in % 16 == 0) && ((a->pitch * sizeof(REAL)) % 16 == 0) && a->nx >= 8;
+    if (peer.cfl_done && !pair_ok) return fail(ADV_ERR_STATE, "the device-resident time step needs the pair kernel");
     if (pair_ok) {
         typedef BurgersPairSmem<REAL> S;
         CUtensorMap tm;
@@ -486,6 +489,16 @@ extern "C" int adv_burgers3d_stage_f32(const adv_stage_args* a, const float* u_i
 // ------------------------------------------------------------------------------------------
 // solver handle
 // ------------------------------------------------------------------------------------------
+// dynamic-CFL state on the device (second half of the arena's flag block) and what the host sees of it
+struct CflDevState {
+    double dt, t, it, tEnd, cfl, dx;        // REAL-valued, widened
+    int done, max_steps;
+    unsigned long long local_max;           // bits of max|u| over what this rank's stage-3 kernels stored
+    unsigned long long global_max;          // after the all-reduce over ranks
+    unsigned seq;                           // dt kernels executed
+};
+struct CflHostStatus { volatile unsigned seq; volatile int done; volatile double t, dt, it; };
+
 struct adv_solver {
     adv_desc d;
     size_t esz;                 // sizeof(REAL)
@@ -507,6 +520,11 @@ struct adv_solver {
     int p2p;                    // 1: halo planes are stored straight into the neighbours' ghost planes
     unsigned stage_counter;     // stages executed so far (the value the halo flags carry)
     unsigned probe_counter;     // exchanges run by adv_halo_probe (carried by the probe flags)
+    // dynamic CFL run (adv_run_until_cfl): the time-step state lives in the flag block of the arena; the host
+    // follows it through a few words of mapped pinned memory that the dt kernel writes
+    bool cfl_on;
+    struct CflHostStatus* cfl_host;     // mapped pinned
+    struct CflHostStatus* cfl_host_dev; // the same words as the device sees them
     // small single-rank problems are launch-bound: three time steps (one full rotation of the three
     // buffers, nine stage launches) are captured once into a CUDA graph and replayed
     cudaGraphExec_t graph_exec;
@@ -645,12 +663,12 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
         const size_t accb = desc->target == ADV_TARGET_BURGERS3D_MGPU ? (s->pitch * (size_t)s->nzs * s->esz + al - 1) / al * al : 0;
         off += accb;
         s->off_flags = off;
-        off += al;
+        off += 2 * al;                  // 512 B of halo / probe flags + 512 B of dynamic-CFL state
         s->arena_bytes = off;
         CREATE_TRY(cudaMalloc((void**)&s->arena, s->arena_bytes));
         for (int b = 0; b < 3; b++) s->buf[b] = s->arena + s->off_buf[b];
         if (accb) s->rowacc = s->arena + s->off_rowacc;
-        CREATE_TRY(cudaMemset(s->arena + s->off_rowacc, 0, accb + al));
+        CREATE_TRY(cudaMemset(s->arena + s->off_rowacc, 0, accb + 2 * al));
     }
     CREATE_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CREATE_TRY(cudaStreamCreateWithFlags(&s->comm_stream, cudaStreamNonBlocking));
@@ -676,6 +694,7 @@ extern "C" int adv_destroy(adv_solver* s)
     s->comm.destroy();
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     for (int n = 0; n < 2; n++) if (s->peer_base[n] && s->peer_is_ipc[n]) cudaIpcCloseMemHandle(s->peer_base[n]);
+    if (s->cfl_host) cudaFreeHost(s->cfl_host);
     if (s->arena) cudaFree(s->arena);
     if (s->ev_start) cudaEventDestroy(s->ev_start);
     if (s->ev_stop) cudaEventDestroy(s->ev_stop);
@@ -933,6 +952,10 @@ static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in
         break;
     case ADV_TARGET_BURGERS3D_SGPU:
     case ADV_TARGET_BURGERS3D_MGPU:
+        if (s->cfl_on) {
+            CflDevState* cs = (CflDevState*)(s->arena + s->off_flags + 512);
+            peer.cfl_dt = &cs->dt; peer.cfl_done = &cs->done; peer.cfl_umax = &cs->local_max;
+        }
         rc = f64 ? burgers3d_stage_impl<double>(&a, (const double*)in, (const double*)uo, (double*)out, (double*)s->rowacc, st, peer)
                  : burgers3d_stage_impl<float>(&a, (const float*)in, (const float*)uo, (float*)out, (float*)s->rowacc, st, peer);
         break;
@@ -1293,17 +1316,129 @@ static int run_until_cfl_impl(adv_solver* s, double tEnd_d, int max_steps, doubl
     return ADV_OK;
 }
 
+// ---- the same with everything on the device (Burgers 3-D through the pair kernel; any number of ranks) ----
+// Stage 3 of every step folds max|u| of what it stores into the state block (no extra pass over the field); ranks
+// combine their maxima with one 8-byte ncclAllReduce(max); a one-thread kernel turns the global maximum into dt,
+// advances t and `it`, raises `done` once t has reached tEnd, and writes a status line the host can see.  The
+// stage kernels read dt and `done` from the state block.  The host never waits for the step it has just enqueued:
+// it enqueues step k as soon as it has SEEN the status of step k-2 (not done), so the GPU always has the next step
+// queued, and exactly one step beyond the last real one gets enqueued -- on every rank alike, which keeps the halo
+// flag counters of the ranks in step.  That last step's kernels see `done` and write nothing.
+template <typename REAL>
+__global__ void cfl_dt_kernel(CflDevState* st, CflHostStatus* hs, const unsigned long long* gmax)
+{
+    if (!st->done) {
+        REAL t = (REAL)st->t, it = (REAL)st->it;
+        const REAL tEnd = (REAL)st->tEnd;
+        if (!(t < tEnd) || (st->max_steps >= 0 && !(it < st->max_steps))) {
+            st->done = 1;
+        } else {
+            const REAL umax = (REAL)__longlong_as_double((long long)*gmax);
+            REAL dt = (REAL)st->cfl * (REAL)st->dx / umax;          // LFWENO5FDM3d.m:71
+            if ((t + dt) > tEnd) dt = tEnd - t;
+            t += dt; it += 1;
+            st->t = t; st->it = it; st->dt = dt;
+            st->local_max = 0;                                      // stage 3 of this step starts a new maximum
+        }
+    }
+    st->seq += 1;
+    hs->t = st->t; hs->dt = st->dt; hs->it = st->it; hs->done = st->done;
+    __threadfence_system();
+    hs->seq = st->seq;
+    __threadfence_system();
+}
+
+static bool burgers3d_pair_usable(const adv_solver* s)
+{
+    return (s->d.target == ADV_TARGET_BURGERS3D_MGPU || s->d.target == ADV_TARGET_BURGERS3D_SGPU) &&
+           !env_on("ADV_BURGERS_DIRECT") && !env_on("ADV_BURGERS_RING") && get_tmap_encode() != nullptr && s->d.nx >= 8;
+}
+
+template <typename REAL>
+static int run_until_cfl_device_impl(adv_solver* s, double tEnd_d, int max_steps, double* dt_last, double* steps, double* t_reached)
+{
+    if (!s->cfl_host) {
+        CUDA_TRY(cudaHostAlloc((void**)&s->cfl_host, sizeof(CflHostStatus), cudaHostAllocMapped));
+        CUDA_TRY(cudaHostGetDevicePointer((void**)&s->cfl_host_dev, (void*)s->cfl_host, 0));
+    }
+    memset((void*)s->cfl_host, 0, sizeof(CflHostStatus));
+    CflDevState* cs = (CflDevState*)(s->arena + s->off_flags + 512);
+    CflDevState h0;
+    memset(&h0, 0, sizeof(h0));
+    h0.tEnd = (double)(REAL)tEnd_d; h0.cfl = (double)(REAL)s->d.coef; h0.dx = (double)(REAL)s->dx; h0.max_steps = max_steps;
+    CUDA_TRY(cudaMemcpyAsync(cs, &h0, sizeof(h0), cudaMemcpyHostToDevice, s->stream));
+    // the first step's maximum: one reduction pass over the slab (later ones come out of stage 3)
+    const long long rows = (long long)s->urows * s->nzs;
+    const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+    absmax_kernel<REAL><<<grid, 256, 0, s->stream>>>((const REAL*)s->buf[s->cur], s->d.nx, (long long)s->pitch, rows, &cs->local_max);
+    CUDA_TRY(cudaGetLastError());
+    s->launches++;
+    const int cur0 = s->cur;
+    s->cfl_on = true;
+    int rc = ADV_OK;
+    unsigned enq = 0;
+    auto enqueue_step = [&]() -> int {
+        const unsigned long long* gmax = &cs->local_max;
+        if (s->d.nranks > 1) {
+            int r = s->comm.allreduce_max_u64(&cs->local_max, &cs->global_max, s->stream, g_err, sizeof(g_err));
+            if (r) return r;
+            gmax = &cs->global_max;
+        }
+        cfl_dt_kernel<REAL><<<1, 1, 0, s->stream>>>(cs, s->cfl_host_dev, gmax);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return fail(ADV_ERR_CUDA, "cfl_dt_kernel: %s", cudaGetErrorString(e));
+        s->launches++;
+        enq++;
+        return do_step(s, 0.0);         // dt comes from the state block
+    };
+    // steps 1 and 2 unconditionally; step k (k >= 3) once the status of step k-2 has been seen and is not `done`
+    for (int k = 0; k < 2 && !rc; k++) rc = enqueue_step();
+    while (!rc) {
+        const unsigned need = enq - 1;                      // about to enqueue step enq+1: wants the status of step enq-1
+        unsigned long long spins = 0;
+        while (s->cfl_host->seq < need) {
+            if ((++spins & 0xfffff) == 0 && cudaStreamQuery(s->stream) != cudaErrorNotReady && s->cfl_host->seq < need) {
+                rc = fail(ADV_ERR_CUDA, "dynamic CFL run: the stream stopped without a status update (%s)", cudaGetErrorString(cudaGetLastError()));
+                break;
+            }
+        }
+        if (rc) break;
+        // The status words may already belong to a later step than `need`.  `done` is sticky and a step is real
+        // exactly when it raised `it`, so "step `need` was not real" <=> done && it < need -- whichever later
+        // status is read, every rank derives the same answer and enqueues the same number of steps.
+        if (s->cfl_host->done && (double)need > s->cfl_host->it) break;
+        rc = enqueue_step();
+    }
+    s->cfl_on = false;
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    const double it = s->cfl_host->it;
+    s->cur = (cur0 + (int)((long long)it % 3)) % 3;         // steps past the end wrote nothing
+    if (dt_last) *dt_last = s->cfl_host->dt;
+    if (steps) *steps = it;
+    if (t_reached) *t_reached = s->cfl_host->t;
+    return ADV_OK;
+}
+
 extern "C" int adv_run_until_cfl(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached)
 {
     if (!s) return fail(ADV_ERR_INVALID, "NULL solver");
     if (!s->uploaded) return fail(ADV_ERR_STATE, "adv_run_until_cfl before adv_upload");
     if (is_heat(s->d.target)) return fail(ADV_ERR_INVALID, "the dynamic CFL step applies to the Burgers targets");
-    if (s->d.nranks > 1) return fail(ADV_ERR_INVALID, "adv_run_until_cfl needs nranks == 1 (the max|u| all-reduce across ranks is not wired yet)");
+    const bool on_device = burgers3d_pair_usable(s) && !env_on("ADV_CFL_HOST_DT");
+    if (s->d.nranks > 1 && !on_device)
+        return fail(ADV_ERR_INVALID, "adv_run_until_cfl with nranks > 1 needs the 3-D Burgers pair kernel (device-resident time step)");
     CUDA_TRY(cudaSetDevice(s->d.device));
     CUDA_TRY(cudaEventRecord(s->ev_start, s->stream));
-    int rc = s->esz == 8 ? run_until_cfl_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
+    int rc;
+    if (on_device)
+        rc = s->esz == 8 ? run_until_cfl_device_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
+                         : run_until_cfl_device_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
+    else
+        rc = s->esz == 8 ? run_until_cfl_impl<double>(s, tEnd, max_steps, dt_last, steps, t_reached)
                          : run_until_cfl_impl<float>(s, tEnd, max_steps, dt_last, steps, t_reached);
     if (rc) return rc;
+    if ((rc = halo_quiesce(s))) return rc;
     CUDA_TRY(cudaEventRecord(s->ev_stop, s->stream));
     return ADV_OK;
 }

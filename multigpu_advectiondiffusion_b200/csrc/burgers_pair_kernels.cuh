@@ -102,6 +102,7 @@ struct BurgersPairSmem {
     Exch ex;
     alignas(16) REAL edge_hn_x[2][TY], edge_hp_x[2][TY];    // hn of column -1, hp of column TX (rows 2t, 2t+1 read as one pair)
     unsigned long long bar, full[2], pro;
+    REAL dt;                                    // the time step: the launch argument, or the device-resident one of a dynamic CFL run
     static_assert(sizeof(Exch) >= RAWB, "the exchange block doubles as a landing zone of the run-in planes");
     // landing zones of the chunk's five run-in planes: raw[0], raw[1], ex, and slot[5] (one or two boxes)
     static constexpr int NLAND = (2 * RAWB <= (int)sizeof(Slot)) ? 5 : 4;
@@ -124,6 +125,9 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     const int kb = a.kb + blockIdx.z * chunk;
     const int ke = min(kb + chunk, a.ke);
     if (kb >= ke) return;
+    if (a.cfl_done && *a.cfl_done) return;  // dynamic CFL run that has reached tEnd: a speculatively enqueued step writes nothing
+    const bool track = (STAGE == 3) && a.cfl_umax != nullptr;
+    unsigned long long umax_bits = 0;       // max |value stored| by this thread (stage 3 of a dynamic CFL run)
     const long long P = a.pitch, Z = a.plane;
     const REAL* __restrict__ wc = a.wc;
     const unsigned bar = (unsigned)__cvta_generic_to_shared(&sm.bar);
@@ -132,6 +136,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     const bool interior = (i0 >= 3) && (i0 + TX - 1 <= a.nx - 4) && (j0 >= 3) && (j0 + TY - 1 <= a.ny - 4);
 
     if (tid == 0) {
+        sm.dt = a.cfl_done ? (REAL)*a.cfl_dt : a.dt;    // read from shared memory where it is used: no register held across the loop
         mbar_init(bar, NW);              // one arrival per warp: lane 0, after __syncwarp()
         mbar_init(pro, 1);
         mbar_init(full0, 1);
@@ -336,10 +341,11 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
                         }
                     }
                     const bool rk = (MODE == BMODE_MGPU) ? true : own_m;
-                    const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
+                    const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, sm.dt, wc);
                     const REAL val = rk ? res : u_m[c];
                     out[o] = val;
                     if (PEER) a.out2[o + a.off2] = val;
+                    if (track) { const unsigned long long vb = (unsigned long long)__double_as_longlong(fabs((double)val)); umax_bits = vb > umax_bits ? vb : umax_bits; }
                 } else {
                     const bool xa = (act >> (4 * c)) & 1u, ya = (act >> (4 * c)) & 2u, za = (act >> (4 * c)) & 4u;
                     const bool row2 = (act >> (4 * c)) & 8u;
@@ -364,10 +370,11 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
                                 if (m >= a.quirk_lo && m <= a.quirk_hi) Lu += term;
                             }
                         }
-                        const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, a.dt, wc);
+                        const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, sm.dt, wc);
                         const REAL val = rk ? res : u_m[c];
                         out[o] = val;
                         if (PEER) a.out2[o + a.off2] = val;
+                        if (track) { const unsigned long long vb = (unsigned long long)__double_as_longlong(fabs((double)val)); umax_bits = vb > umax_bits ? vb : umax_bits; }
                     }
                 }
             }
@@ -458,6 +465,14 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         for (; p <= ke; p++, n++) iteration(rim_tag, BoolTag<false>(), PR(), p, n);
     };
     if (interior) run(BoolTag<false>()); else run(BoolTag<true>());
+    if (track) {                            // one atomic per warp
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, umax_bits, o);
+            umax_bits = other > umax_bits ? other : umax_bits;
+        }
+        if (tx == 0) atomicMax(a.cfl_umax, umax_bits);
+    }
 }
 
 }  // namespace adv

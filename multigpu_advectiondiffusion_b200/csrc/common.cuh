@@ -66,6 +66,12 @@ struct BurgersArgs {
     // the pair kernel's copy of [0..8] with the k = 0 entries divided by sqrt(2) (JS): P_0 arrives halved, which
     // turns 2*d01*n0 + d12*n2 over n0+n1+n2 into d01*n0 + d12*n2' over n0/2 + n1' + n2' (one addition less)
     REAL wp[9];
+    // dynamic CFL step (adv_run_until_cfl): when cfl_done is non-null the kernel returns at once if *cfl_done,
+    // takes dt from *cfl_dt instead of the `dt` argument, and (stage 3, cfl_umax non-null) folds max|u_out| of
+    // everything it stores into *cfl_umax (IEEE bits of a non-negative double order like the values)
+    const double* cfl_dt;
+    const int* cfl_done;
+    unsigned long long* cfl_umax;
 };
 
 template <typename REAL>

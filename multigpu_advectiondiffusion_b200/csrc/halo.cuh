@@ -31,6 +31,7 @@ struct NcclApi {
     int (*CommDestroy)(comm_t);
     int (*Send)(const void*, size_t, int, int, comm_t, cudaStream_t);
     int (*Recv)(void*, size_t, int, int, comm_t, cudaStream_t);
+    int (*AllReduce)(const void*, void*, size_t, int, int, comm_t, cudaStream_t);
     int (*GroupStart)();
     int (*GroupEnd)();
     const char* (*GetErrorString)(int);
@@ -56,6 +57,7 @@ struct NcclApi {
         NCCL_SYM(CommDestroy, "ncclCommDestroy")
         NCCL_SYM(Send, "ncclSend")
         NCCL_SYM(Recv, "ncclRecv")
+        NCCL_SYM(AllReduce, "ncclAllReduce")
         NCCL_SYM(GroupStart, "ncclGroupStart")
         NCCL_SYM(GroupEnd, "ncclGroupEnd")
         NCCL_SYM(GetErrorString, "ncclGetErrorString")
@@ -97,6 +99,17 @@ struct HaloComm {
     {
         if (api && comm) api->CommDestroy(comm);
         comm = nullptr;
+    }
+
+    // max over ranks of one non-negative double given by its IEEE bits (ordered like the values): the dynamic
+    // CFL step's max|u| (LFWENO5FDM3d.m:71 takes it over the whole field)
+    int allreduce_max_u64(const unsigned long long* src, unsigned long long* dst, cudaStream_t st, char* err, size_t errlen)
+    {
+        if (!comm) { snprintf(err, errlen, "all-reduce without a communicator"); return ADV_ERR_COMM; }
+        const int kUint64 = 5, kMax = 2;    // ncclUint64, ncclMax
+        int rc = api->AllReduce(src, dst, 1, kUint64, kMax, comm, st);
+        if (rc) { snprintf(err, errlen, "ncclAllReduce: %s", api->GetErrorString(rc)); return ADV_ERR_COMM; }
+        return ADV_OK;
     }
 
     // field: this rank's stored slab (nzs planes of plane_elems elements); exchanges 3 planes per side

@@ -237,6 +237,50 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         print("MP_OK gpu %s P=%d halo=%s bit-exact vs P=1, rel err vs oracle %.2e" % (target, P, halo, err))
 
 
+def run_gpu_cfl(rank, P, nx, ny, nz, tEnd, halo):
+    """adv_run_until_cfl on P ranks (SURVEY 8f-2): the max|u| of every step is combined across ranks on the device;
+    all ranks must take the same steps, and the merged field must equal the 1-rank run bit for bit."""
+    import multigpu_advectiondiffusion_b200 as adv
+    torch.cuda.set_device(rank)
+    idb = [None]
+    if rank == 0:
+        buf = (C.c_ubyte * 128)()
+        adv._lib.check(adv.lib().adv_comm_unique_id(C.byref(buf)))
+        idb = [bytes(buf)]
+    dist.broadcast_object_list(idb, 0)
+    g = 0.8 * orc.ic_burgers3d_mgpu(nx, ny, nz)
+    g0, g1 = slab_bounds(nz, P, rank)
+    with adv.Solver("burgers3d_mgpu", nx, ny, nz, coef=0.3, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
+        if halo == "peer":
+            hs = [None] * P
+            dist.all_gather_object(hs, s.peer_handle())
+            s.peer_connect(hs[rank - 1] if rank > 0 else None, hs[rank + 1] if rank < P - 1 else None)
+        s.upload(g[g0:g1].copy())
+        info = s.run_until_cfl(tEnd)
+        u = s.download()
+    infos = [None] * P if rank == 0 else None
+    dist.gather_object(info, infos, dst=0)
+    parts = [None] * P if rank == 0 else None
+    dist.gather_object(u, parts, dst=0)
+    if rank == 0:
+        assert all(i == infos[0] for i in infos), infos
+        merged = g.copy()
+        nzl = nz // P
+        for r in range(P):
+            merged[r * nzl + 3: r * nzl + 3 + nzl] = parts[r][3:3 + nzl]
+        with adv.Solver("burgers3d_mgpu", nx, ny, nz, coef=0.3, device=0) as s1:
+            s1.upload(g)
+            i1 = s1.run_until_cfl(tEnd)
+            one = s1.download()
+        one[:3], one[-3:] = g[:3], g[-3:]
+        assert i1 == infos[0], (i1, infos[0])
+        assert np.array_equal(merged, one), "dynamic CFL: P=%d differs from P=1: %g" % (P, float(np.abs(merged - one).max()))
+        want, wi = orc.burgers3d_mgpu_cfl(g, tEnd)
+        err = orc.rel_err(merged, want)
+        assert wi["it"] == i1["it"] and err <= 1e-12, (wi, i1, err)
+        print("MP_OK gpu_cfl burgers3d_mgpu P=%d halo=%s %d dynamic steps, bit-exact vs P=1, rel err vs oracle %.2e" % (P, halo, int(i1["it"]), err))
+
+
 def main():
     mode = sys.argv[1]
     rank, P = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -252,6 +296,7 @@ def main():
                 for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5),
                                              ("burgers2d_mgpu", (72, 96, 1), 3), ("heat2d_mgpu", (70, 96, 1), 5)):
                     run_gpu(rank, P, target, *shape, steps, halo=halo)
+                run_gpu_cfl(rank, P, 40, 36, 48, 0.15, halo)
     finally:
         dist.barrier()
         dist.destroy_process_group()

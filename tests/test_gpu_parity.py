@@ -288,21 +288,45 @@ def test_gpu_reproduces_the_reference_accuracy_log_3d():
         assert "%.2e" % (dx**3 * err.sum()) == "%.2e" % l1 and "%.2e" % err.max() == "%.2e" % linf, (n, dx**3 * err.sum(), err.max())
 
 
-def test_dynamic_cfl_time_step_vs_oracle():
-    """adv_run_until_cfl: dt = CFL*dx/max|u| recomputed every step from a device reduction."""
+def test_dynamic_cfl_time_step_vs_oracle(monkeypatch):
+    """adv_run_until_cfl: dt = CFL*dx/max|u| recomputed every step (LFWENO5FDM3d.m:71).  Default path:
+    everything on the device -- max|u| folded into stage 3, dt computed by a one-thread kernel, the host only follows
+    a status word; ADV_CFL_HOST_DT=1: the first version (separate reduction pass, dt computed on the host).  Same
+    arithmetic, so the two give the same bits; both within 1e-12 of the oracle."""
     nx, ny, nz = 40, 36, 32
     u0 = 0.8 * orc.ic_burgers3d_mgpu(nx, ny, nz)
     tEnd = 0.15                     # 8 dynamic steps (the last one 0.0139 long, far from a borderline count), 10 fixed ones
     want, wi = orc.burgers3d_mgpu_cfl(u0, tEnd)
     _, fixed = orc.burgers3d_mgpu(u0, tEnd)
+    results = {}
+    for mode in ("device", "host"):
+        if mode == "host":
+            monkeypatch.setenv("ADV_CFL_HOST_DT", "1")
+        else:
+            monkeypatch.delenv("ADV_CFL_HOST_DT", raising=False)
+        with adv.Solver("burgers3d_mgpu", nx, ny, nz, coef=0.3) as s:
+            s.upload(u0)
+            gi = s.run_until_cfl(tEnd)
+            got = s.download()
+            # the solver is usable afterwards: two more fixed-dt steps run from the buffer the dynamic run ended in
+            s.step(2)
+            after = s.download()
+        got[:3], got[-3:] = u0[:3], u0[-3:]
+        assert gi["it"] == wi["it"] == 8 and fixed["it"] == 10
+        assert abs(gi["t"] - tEnd) < 1e-12 and abs(gi["dt"] / wi["dt"] - 1) < 1e-9
+        assert rel(got, want) <= 1e-12, (mode, rel(got, want))
+        results[mode] = (got, after)
+    monkeypatch.delenv("ADV_CFL_HOST_DT", raising=False)
+    assert np.array_equal(results["device"][0], results["host"][0])
+    assert np.array_equal(results["device"][1], results["host"][1])
+    # a step budget ends the run as well (max_steps), on the device path too
     with adv.Solver("burgers3d_mgpu", nx, ny, nz, coef=0.3) as s:
         s.upload(u0)
-        gi = s.run_until_cfl(tEnd)
-        got = s.download()
-    got[:3], got[-3:] = u0[:3], u0[-3:]
-    assert gi["it"] == wi["it"] == 8 and fixed["it"] == 10
-    assert abs(gi["t"] - tEnd) < 1e-12 and abs(gi["dt"] / wi["dt"] - 1) < 1e-9
-    assert rel(got, want) <= 1e-11
+        gi = s.run_until_cfl(tEnd, max_steps=3)
+        got3 = s.download()
+    want3, wi3 = orc.burgers3d_mgpu_cfl(u0, tEnd, max_steps=3)
+    got3[:3], got3[-3:] = u0[:3], u0[-3:]
+    assert gi["it"] == wi3["it"] == 3 and rel(got3, want3) <= 1e-12
     with adv.Solver("heat3d_mgpu", nx, ny, nz, coef=1.0) as h:
         h.upload(u0)
         with pytest.raises(adv.AdvError):
