@@ -448,6 +448,24 @@ def run_gpu_workload(name, ctx, steps, warmup, precision, halo_mode, with_e2e, w
                "h2d_bytes_per_step": int(hnp.nbytes), "d2h_bytes_per_step": int(hnp.nbytes),
                "definition": "one e2e step = adv_upload(pinned host slab) + %d time steps + adv_download, as one run of the reference driver" % S,
                "steps_per_call": S, "calls": reps}
+        # where the end-to-end time goes: the two host copies timed alone, every rank copying at the same moment
+        # (as in the loop above), beside the device time of the S steps.  With N ranks on one host the copies share
+        # the host's memory and PCIe root complexes, so their per-GPU rate falls as N grows while the kernels' does not.
+        barrier()
+        t0 = time.perf_counter()
+        s.upload(hnp)
+        barrier()
+        t_up = max_over_ranks(time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        s.download(hnp)
+        barrier()
+        t_down = max_over_ranks(time.perf_counter() - t0)
+        t_comp = S * (ms / steps) * 1e-3
+        e2e["breakdown"] = {"h2d_s": t_up, "d2h_s": t_down, "device_steps_s": t_comp, "sum_s": t_up + t_down + t_comp,
+                            "measured_s_per_call": te / reps,
+                            "h2d_GBps_per_gpu": hnp.nbytes / t_up / 1e9, "d2h_GBps_per_gpu": hnp.nbytes / t_down / 1e9,
+                            "host_copy_GBps_all_gpus": (world if nranks > 1 or w["scaling"] == "replicas" else 1) * 2 * hnp.nbytes / (t_up + t_down) / 1e9,
+                            "copy_share_of_call": (t_up + t_down) / (t_up + t_down + t_comp)}
         del host, hnp
 
     s.close()

@@ -84,6 +84,21 @@ def main():
         o = np.fromfile(os.path.join(d_our, "result.bin"), dtype=np.float32)
         out["heat2d_512"] = {"reference_sm100": ref, "this_repo": our, "speedup": our["Mcell_updates_per_s"] / ref["Mcell_updates_per_s"],
                              "result_bin_max_abs_diff_1000_steps": float(np.abs(r - o).max())}
+        # ---- the remaining single-GPU comparators BASELINE.json's configs name (reference side only: this repo's
+        # side is the same driver as above): Diffusion3d_PitchedMem, Diffusion2d_PitchedMem, Burgers3d_WENO5_SharedMem
+        # (built with its one unused texture<> declaration dropped, oracle/Makefile)
+        if os.path.exists(os.path.join(REF, "ref_diffusion3d_pitched.run")):
+            a = lambda it: ["1.0", "10", "10", "10", str(n), str(n), str(n), str(it), "32", "4", "4"]
+            out["heat3d_PitchedMem"] = {"reference_sm100": diff_rate([os.path.join(REF, "ref_diffusion3d_pitched.run")], a(1000), a(5000), cells, 1000, 5000, d_ref)}
+        if os.path.exists(os.path.join(REF, "ref_diffusion2d_pitched.run")):
+            a = lambda it: ["1.0", "10", "10", "512", "512", str(it), "16", "16"]
+            out["heat2d_PitchedMem_512"] = {"reference_sm100": diff_rate([os.path.join(REF, "ref_diffusion2d_pitched.run")], a(50000), a(250000), 512 * 512, 50000, 250000, d_ref)}
+        if os.path.exists(os.path.join(REF, "ref_burgers3d_shared.run")):
+            a = lambda tend: [str(tend), "0.3", "2", "2", "2", str(n), str(n), str(n)]
+            a11 = lambda tend: a(tend) + ["8", "8", "8"]
+            _, o1 = wall([os.path.join(DRV, "burgers3d.run")] + a11(1.0), d_our)
+            _, o2 = wall([os.path.join(DRV, "burgers3d.run")] + a11(3.0), d_our)
+            out["burgers3d_WENO5_SharedMem"] = {"reference_sm100": diff_rate([os.path.join(REF, "ref_burgers3d_shared.run")], a(1.0), a(3.0), cells, steps_of(o1), steps_of(o2), d_ref)}
     print(json.dumps(out))
 
 
