@@ -82,8 +82,21 @@ static bool is_2d_mgpu(int t) { return t == ADV_TARGET_HEAT2D_MGPU || t == ADV_T
 static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU || is_2d_mgpu(t); }
 
 // second destination of a stage launch (fused halo exchange); internal, not part of the public stage ABI
-struct PeerOut { void* out2; long long off2; const double* cfl_dt; const int* cfl_done; unsigned long long* cfl_umax; };
-static const PeerOut kNoPeer = {nullptr, 0, nullptr, nullptr, nullptr};
+struct PeerOut {
+    void* out2; long long off2;
+    const double* cfl_dt; const int* cfl_done; unsigned long long* cfl_umax;
+    const SlabSched* fused;     // one launch per stage: boundary windows + flags (interior window = the stage args' [k_begin,k_end))
+};
+static const PeerOut kNoPeer = {nullptr, 0, nullptr, nullptr, nullptr, nullptr};
+
+// launch schedule of a stage: the caller's fused boundary windows (if any) + the interior window in chunks
+static SlabSched make_sched(const SlabSched* fused, int kb, int ke, int chunk)
+{
+    SlabSched sc;
+    if (fused) sc = *fused; else memset(&sc, 0, sizeof(sc));
+    sc.ib = kb; sc.ie = ke; sc.chunk = chunk;
+    return sc;
+}
 
 static int check_stage_args(const adv_stage_args* a, const void* u_in, const void* uo, const void* u_out, int min_n)
 {
@@ -172,7 +185,8 @@ static int encode_tmap3(CUtensorMap* tm, int esz, const void* base, int nx, int 
 }
 
 template <typename REAL, int TY, int NST>
-static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st)
+static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, const REAL* u_in, const REAL* uo, REAL* u_out, cudaStream_t st,
+                             const SlabSched* fused = nullptr)
 {
     typedef HeatTmaSmem<REAL, TY, NST> S;
     CUtensorMap tm, tmo;
@@ -186,13 +200,14 @@ static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, c
     int nch = nch_env > 0 ? nch_env : (2368 + gx * gy - 1) / (gx * gy);
     if (nch > planes / 16) nch = planes / 16;
     if (nch < 1) nch = 1;
-    const int chunk = (planes + nch - 1) / nch;
-    dim3 grid(gx, gy, (planes + chunk - 1) / chunk), block(32, TY + 1, 1);
+    const int chunk = planes > 0 ? (planes + nch - 1) / nch : 1;
+    const SlabSched sc = make_sched(fused, a->k_begin, a->k_end, chunk);
+    dim3 grid(gx, gy, sc.nb + (planes + chunk - 1) / chunk), block(32, TY + 1, 1);
     const size_t shm = sizeof(S);
 #define HEAT_TMA_LAUNCH(STAGE_) do { \
         auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_>; \
         if (shm > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-        kfn<<<grid, block, shm, st>>>(tm, tmo, h, chunk, u_out); } while (0)
+        kfn<<<grid, block, shm, st>>>(tm, tmo, h, sc, u_out); } while (0)
     if (a->stage == 1) HEAT_TMA_LAUNCH(1); else if (a->stage == 2) HEAT_TMA_LAUNCH(2); else HEAT_TMA_LAUNCH(3);
 #undef HEAT_TMA_LAUNCH
     CUDA_TRY(cudaGetLastError());
@@ -213,7 +228,7 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     int rc = check_stage_args(a, u_in, uo, u_out, 5);
     if (rc) return rc;
     if (a->k_begin < 0 || a->k_end > a->nzs || a->k_begin > a->k_end) return fail(ADV_ERR_INVALID, "bad plane window [%d,%d) of %d", a->k_begin, a->k_end, a->nzs);
-    if (a->k_begin == a->k_end) return ADV_OK;
+    if (a->k_begin == a->k_end && !peer.fused) return ADV_OK;
     HeatArgs<REAL> h;
     rc = heat_args_from<REAL>(a, h);
     if (rc) return rc;
@@ -221,8 +236,8 @@ static int heat3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     // TMA path: needs 16-byte rows and pairs of cells; anything else takes the direct kernel
     const int heat_variant = env_on("ADV_HEAT_DIRECT") ? 0 : 1;     // A/B switch: ADV_HEAT_DIRECT=1 forces the direct kernel
     const bool tma_ok = heat_variant > 0 && heat3d_tma_ok<REAL>(a, u_in, uo, u_out);
-    if (peer.out2 && !tma_ok) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
-    if (tma_ok) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st);     // 64x8 tile, 6 planes in flight
+    if ((peer.out2 || peer.fused) && !tma_ok) return fail(ADV_ERR_INVALID, "fused halo stores need the TMA heat kernel (even nx, 16-byte rows)");
+    if (tma_ok) return heat3d_launch_tma<REAL, 8, 6>(a, h, u_in, uo, u_out, st, peer.fused);     // 64x8 tile, 6 planes in flight
     constexpr int CHUNK = 32;
     dim3 block(32, 8, 1);
     dim3 grid((a->nx + 31) / 32, (a->ny + 7) / 8, (a->k_end - a->k_begin + CHUNK - 1) / CHUNK);
@@ -259,7 +274,7 @@ static int heat2d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h2d,
     const size_t shm = sizeof(S);
 #define HEAT2D_TMA_LAUNCH(STAGE_) do { \
         auto kfn = heat3d_stage_tma<REAL, TY, NST, STAGE_, true>; \
-        kfn<<<grid, block, shm, st>>>(tm, tmo, h, chunk, u_out); } while (0)
+        kfn<<<grid, block, shm, st>>>(tm, tmo, h, make_sched(nullptr, h.kb, h.ke, chunk), u_out); } while (0)
     if (a->stage == 1) HEAT2D_TMA_LAUNCH(1); else if (a->stage == 2) HEAT2D_TMA_LAUNCH(2); else HEAT2D_TMA_LAUNCH(3);
 #undef HEAT2D_TMA_LAUNCH
     CUDA_TRY(cudaGetLastError());
@@ -367,7 +382,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     if (rc) return rc;
     if (a->k_begin < 0 || a->k_end > a->nzs || a->k_begin > a->k_end) return fail(ADV_ERR_INVALID, "bad plane window [%d,%d) of %d", a->k_begin, a->k_end, a->nzs);
     if (a->own_lo < 3 || a->own_hi > a->nzs - 3) return fail(ADV_ERR_INVALID, "owned planes [%d,%d) need 3 planes of halo inside [0,%d)", a->own_lo, a->own_hi, a->nzs);
-    if (a->k_begin == a->k_end) return ADV_OK;
+    if (a->k_begin == a->k_end && !peer.fused) return ADV_OK;
     const bool mg = a->target == ADV_TARGET_BURGERS3D_MGPU;
     if (!mg && a->target != ADV_TARGET_BURGERS3D_SGPU) return fail(ADV_ERR_INVALID, "target %d is not a Burgers target", a->target);
     if (mg && !rowacc) return fail(ADV_ERR_INVALID, "rowacc scratch is required for ADV_TARGET_BURGERS3D_MGPU");
@@ -396,7 +411,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     // default: the pair kernel (TMA-staged planes; needs 16-byte rows for the tensor map)
     const bool pair_ok = !force_direct && !env_on("ADV_BURGERS_RING") && get_tmap_encode() != nullptr &&
                          ((uintptr_t)u_in % 16 == 0) && ((a->pitch * sizeof(REAL)) % 16 == 0) && a->nx >= 8;
-    if (peer.cfl_done && !pair_ok) return fail(ADV_ERR_STATE, "the device-resident time step needs the pair kernel");
+    if ((peer.cfl_done || peer.fused) && !pair_ok) return fail(ADV_ERR_STATE, "the device-resident time step and the one-launch stage need the pair kernel");
     if (pair_ok) {
         typedef BurgersPairSmem<REAL> S;
         CUtensorMap tm;
@@ -419,20 +434,21 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
             if (best < 0 || cost < best) { best = cost; nch = c; }
         }
         if (forced > 0) nch = forced;
-        const int chunk = (planes + nch - 1) / nch;
-        dim3 pgrid(gx, gy, (planes + chunk - 1) / chunk), pblock(32, S::NW, 1);
+        const int chunk = planes > 0 ? (planes + nch - 1) / nch : 1;
+        const SlabSched sc = make_sched(peer.fused, a->k_begin, a->k_end, chunk);
+        dim3 pgrid(gx, gy, sc.nb + (planes + chunk - 1) / chunk), pblock(32, S::NW, 1);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
         const size_t shm = sizeof(S);
 #define LAUNCH_PAIR(W_, M_, STAGE_, PEER_) do { \
             auto kfn = burgers3d_stage_pair<REAL, W_, M_, STAGE_, PEER_>; \
             CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
-            kfn<<<pgrid, pblock, shm, st>>>(tm, b, chunk, u_in, uo_, u_out, rowacc); } while (0)
+            kfn<<<pgrid, pblock, shm, st>>>(tm, b, sc, u_in, uo_, u_out, rowacc); } while (0)
 #define LAUNCH_PAIR_S(W_, M_, PEER_) do { \
             if (a->stage == 1) LAUNCH_PAIR(W_, M_, 1, PEER_); \
             else if (a->stage == 2) LAUNCH_PAIR(W_, M_, 2, PEER_); \
             else LAUNCH_PAIR(W_, M_, 3, PEER_); } while (0)
         if (!mg) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, false);
-        else if (b.out2) LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, true);
+        else if (b.out2 || peer.fused) LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, true);
         else LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, false);
 #undef LAUNCH_PAIR_S
 #undef LAUNCH_PAIR
@@ -927,7 +943,8 @@ extern "C" int adv_init_reference_ic_device(adv_solver* s)
 static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out, int kb, int ke,
                              cudaStream_t st, PeerOut peer)
 {
-    if (kb >= ke) return ADV_OK;
+    if (kb >= ke && !peer.fused) return ADV_OK;
+    if (kb > ke) ke = kb;
     adv_stage_args a;
     memset(&a, 0, sizeof(a));
     a.target = s->d.target; a.flags = s->d.flags; a.stage = stage;
@@ -1033,6 +1050,21 @@ static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in
 // locally and, through NVLink peer mappings, into the neighbour's ghost planes; a flag per neighbour
 // says "stage c has landed".  A rank starts stage c once both neighbours have signalled c-1, which is
 // also when they have stopped reading the ghost planes this stage overwrites.  No NCCL, no comm stream.
+// 3-D targets whose stage kernel takes a SlabSched: the whole stage is ONE launch (boundary windows first, flag wait
+// and flag release inside the kernel) instead of two stream waits + two 3-plane launches + two signal kernels + the
+// interior launch.  ADV_HALO_MULTILAUNCH=1 keeps the old schedule (A/B).
+static bool stage_fusable(const adv_solver* s)
+{
+    if (env_on("ADV_HALO_MULTILAUNCH") || !get_tmap_encode()) return false;
+    if (s->d.target == ADV_TARGET_HEAT3D_MGPU)
+        return !env_on("ADV_HEAT_DIRECT") && s->d.nx % 2 == 0 && s->d.nx >= 8;
+    if (s->d.target == ADV_TARGET_BURGERS3D_MGPU)
+        return !env_on("ADV_BURGERS_DIRECT") && !env_on("ADV_BURGERS_RING") && s->d.nx >= 8;
+    return false;
+}
+
+enum { STAGE_TICKET_LEFT = 88, STAGE_TICKET_RIGHT = 92 };
+
 static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, const void* uo, void* out)
 {
     const int P = s->d.nranks, r = s->d.rank, R = ADV_RADIUS;
@@ -1042,6 +1074,32 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
     if (ob < 0) return fail(ADV_ERR_STATE, "stage output is not one of the solver's buffers");
     const long long plane = (long long)s->pitch * s->urows;
     int rc;
+    if (stage_fusable(s)) {
+        unsigned* flags = (unsigned*)(s->arena + s->off_flags);
+        SlabSched f;
+        memset(&f, 0, sizeof(f));
+        f.wait_val = c - 1; f.signal_val = c;
+        if (r > 0) {            // my planes [3,6) are the left neighbour's ghost planes [nzs-3, nzs)
+            const int w = f.nb++;
+            f.wb[w] = R; f.we[w] = 2 * R;
+            f.out2[w] = s->peer_base[0] + s->off_buf[ob]; f.off2[w] = (long long)(s->nzs - 2 * R) * plane;
+            f.wait_flag[w] = flags + FLAG_FROM_LEFT;
+            f.peer_flag[w] = (unsigned*)(s->peer_base[0] + s->off_flags) + FLAG_FROM_RIGHT;
+            f.ticket[w] = flags + STAGE_TICKET_LEFT;
+        }
+        if (r < P - 1) {        // my planes [nzs-6, nzs-3) are the right neighbour's ghost planes [0, 3)
+            const int w = f.nb++;
+            f.wb[w] = s->nzs - 2 * R; f.we[w] = s->nzs - R;
+            f.out2[w] = s->peer_base[1] + s->off_buf[ob]; f.off2[w] = -(long long)(s->nzs - 2 * R) * plane;
+            f.wait_flag[w] = flags + FLAG_FROM_RIGHT;
+            f.peer_flag[w] = (unsigned*)(s->peer_base[1] + s->off_flags) + FLAG_FROM_LEFT;
+            f.ticket[w] = flags + STAGE_TICKET_RIGHT;
+        }
+        PeerOut po = kNoPeer;
+        po.fused = &f;
+        const int flo = (r > 0) ? 2 * R : 0, fhi = (r < P - 1) ? s->nzs - 2 * R : s->nzs;
+        return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, po);
+    }
     if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1))) return rc;
     if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1))) return rc;
     if (r > 0) {            // my planes [3,6) are the left neighbour's ghost planes [nzs-3, nzs)

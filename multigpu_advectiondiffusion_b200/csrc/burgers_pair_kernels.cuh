@@ -110,7 +110,7 @@ struct BurgersPairSmem {
 
 template <typename REAL, int W, int MODE, int STAGE, bool PEER>
 __global__ void __launch_bounds__(256, 2)
-burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL> a, int chunk,
+burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL> a, SlabSched sched,
                      const REAL* __restrict__ u, const REAL* __restrict__ uo, REAL* __restrict__ out, REAL* __restrict__ rowacc)
 {
     typedef BurgersPairSmem<REAL> S;
@@ -122,10 +122,15 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int tid = ty * 32 + tx;
     const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
+    int kb, ke;
+    const int bw = slab_window(sched, kb, ke);          // boundary window (fused halo exchange) or interior chunk
     if (kb >= ke) return;
-    if (a.cfl_done && *a.cfl_done) return;  // dynamic CFL run that has reached tEnd: a speculatively enqueued step writes nothing
+    REAL* const out2 = (REAL*)slab_out2(sched, bw, a.out2);    // PEER: second destination of every store (null: none)
+    const long long off2 = slab_off2(sched, bw, a.off2);
+    if (a.cfl_done && *a.cfl_done) {        // dynamic CFL run that has reached tEnd: a speculatively enqueued step writes nothing,
+        slab_signal(sched, threadIdx.x == 0 && threadIdx.y == 0);   // but keeps the neighbours' stage counters moving
+        return;
+    }
     const bool track = (STAGE == 3) && a.cfl_umax != nullptr;
     unsigned long long umax_bits = 0;       // max |value stored| by this thread (stage 3 of a dynamic CFL run)
     const long long P = a.pitch, Z = a.plane;
@@ -144,6 +149,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    slab_wait(sched, bw, tid == 0);                     // the neighbour's previous stage has landed in our ghost planes
 
     // ---- what this thread stages per plane: its two cells and one or two points of the frame around the tile
     const int ownL = (2 * ty + H) * RP + tx + HXR, ownU = ownL + RP;
@@ -344,7 +350,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
                     const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, sm.dt, wc);
                     const REAL val = rk ? res : u_m[c];
                     out[o] = val;
-                    if (PEER) a.out2[o + a.off2] = val;
+                    if (PEER && out2) out2[o + off2] = val;
                     if (track) { const unsigned long long vb = (unsigned long long)__double_as_longlong(fabs((double)val)); umax_bits = vb > umax_bits ? vb : umax_bits; }
                 } else {
                     const bool xa = (act >> (4 * c)) & 1u, ya = (act >> (4 * c)) & 2u, za = (act >> (4 * c)) & 4u;
@@ -373,7 +379,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
                         const REAL res = rk_stage<REAL, STAGE>(u_m[c], uo_m[c], Lu, sm.dt, wc);
                         const REAL val = rk ? res : u_m[c];
                         out[o] = val;
-                        if (PEER) a.out2[o + a.off2] = val;
+                        if (PEER && out2) out2[o + off2] = val;
                         if (track) { const unsigned long long vb = (unsigned long long)__double_as_longlong(fabs((double)val)); umax_bits = vb > umax_bits ? vb : umax_bits; }
                     }
                 }
@@ -473,6 +479,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         }
         if (tx == 0) atomicMax(a.cfl_umax, umax_bits);
     }
+    slab_signal(sched, tid == 0);                   // last CTA of a boundary window raises the neighbour's flag
 }
 
 }  // namespace adv

@@ -41,6 +41,68 @@ struct HeatArgs {
     long long off2;
 };
 
+// One launch per RK stage on a multi-rank slab (3-D targets): the launch's z chunks are, in this order, up to two
+// BOUNDARY windows (the 3 planes next to each neighbour: computed first, stored locally and into the neighbour's
+// ghost planes through the NVLink mapping) and then the chunks of the interior window.  A boundary window first
+// waits (one thread spins, the CTA follows) until the neighbour has raised this rank's flag to wait_val -- its
+// previous stage has landed in our ghost planes and it has stopped reading the ghost planes we are about to
+// overwrite -- and the last of its CTAs to finish raises the neighbour's flag to signal_val.  nb == 0: plain launch.
+struct SlabSched {
+    int nb;                             // boundary windows in this launch: blockIdx.z = 0 .. nb-1
+    int wb[2], we[2];                   // their plane ranges [wb, we)
+    void* out2[2];                      // second destination of a boundary window (neighbour's arena buffer)
+    long long off2[2];                  // element offset of its ghost planes relative to our planes
+    const unsigned* wait_flag[2];       // local flag word the window waits on (null: no wait)
+    unsigned* peer_flag[2];             // neighbour's flag word the window raises when complete
+    unsigned* ticket[2];                // local CTA counters (zero between launches)
+    unsigned wait_val, signal_val;
+    int ib, ie, chunk;                  // interior window and its chunk length
+};
+
+// window of this CTA: returns the boundary index (0/1) or -1 for an interior chunk.  (The two-element arrays are
+// read with selects, never with a run-time index: the struct stays in the kernel-parameter constant bank.)
+__device__ __forceinline__ int slab_window(const SlabSched& sc, int& kb, int& ke)
+{
+    const int z = blockIdx.z;
+    if (z < sc.nb) { kb = z ? sc.wb[1] : sc.wb[0]; ke = z ? sc.we[1] : sc.we[0]; return z; }
+    kb = sc.ib + (z - sc.nb) * sc.chunk;
+    ke = min(kb + sc.chunk, sc.ie);
+    return -1;
+}
+__device__ __forceinline__ void* slab_out2(const SlabSched& sc, int bw, void* dflt) { return bw < 0 ? dflt : (bw ? sc.out2[1] : sc.out2[0]); }
+__device__ __forceinline__ long long slab_off2(const SlabSched& sc, int bw, long long dflt) { return bw < 0 ? dflt : (bw ? sc.off2[1] : sc.off2[0]); }
+__device__ __forceinline__ void slab_wait(const SlabSched& sc, int bw, bool leader)
+{
+    if (bw < 0) return;
+    const volatile unsigned* f = bw ? sc.wait_flag[1] : sc.wait_flag[0];
+    if (!f) return;
+    if (leader) {
+        while ((int)(*f - sc.wait_val) < 0) __nanosleep(64);
+        __threadfence();
+    }
+    __syncthreads();
+}
+// call with every thread of the CTA, after its last store (the window is taken from blockIdx again so that
+// nothing has to stay in a register across the kernel's main loop)
+__device__ __forceinline__ void slab_signal(const SlabSched& sc, bool leader)
+{
+    const int z = blockIdx.z;
+    if (z >= sc.nb) return;
+    __threadfence_system();             // this thread's peer stores are visible system-wide before the ticket
+    __syncthreads();
+    if (leader) {
+        unsigned* ticket = z ? sc.ticket[1] : sc.ticket[0];
+        unsigned* flag = z ? sc.peer_flag[1] : sc.peer_flag[0];
+        const unsigned n = gridDim.x * gridDim.y;
+        if (atomicAdd(ticket, 1u) == n - 1) {
+            *ticket = 0;
+            __threadfence_system();
+            *(volatile unsigned*)flag = sc.signal_val;
+            __threadfence_system();
+        }
+    }
+}
+
 enum { WENO_JS = 0, WENO_Z = 1 };
 enum { BMODE_SGPU = 0, BMODE_MGPU = 1 };
 

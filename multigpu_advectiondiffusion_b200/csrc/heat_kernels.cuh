@@ -236,7 +236,7 @@ struct HeatTmaSmem {
 template <typename REAL, int TY, int NST, int STAGE, bool TWO_D = false>
 __global__ void __launch_bounds__(32 * (TY + 1))
 heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_uo,
-                  HeatArgs<REAL> a, int chunk, REAL* __restrict__ out)
+                  HeatArgs<REAL> a, SlabSched sched, REAL* __restrict__ out)
 {
     typedef typename Vec2T<REAL>::type V2;
     typedef HeatTmaSmem<REAL, TY, NST, TWO_D> S;
@@ -247,9 +247,11 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
 
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
-    const int kb = a.kb + blockIdx.z * chunk;
-    const int ke = min(kb + chunk, a.ke);
+    int kb, ke;
+    const int bw = slab_window(sched, kb, ke);          // boundary window (fused halo exchange) or interior chunk
     if (kb >= ke) return;
+    REAL* const out2 = (REAL*)slab_out2(sched, bw, a.out2);
+    const long long off2 = slab_off2(sched, bw, a.off2);
     const int p_first = kb - 2;
     const int N = (ke + 1) - p_first + 1;                   // planes to stream: kb-2 .. ke+1
 
@@ -261,6 +263,7 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    slab_wait(sched, bw, tx == 0 && ty == 0);           // the neighbour's previous stage has landed in our ghost planes
 
     if (ty == TY) {
         // ---------------- producer warp ----------------
@@ -276,6 +279,7 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 if (with_old) tma_load_3d((unsigned)__cvta_generic_to_shared(&sm.old[s].v[0][0]), &tmap_uo, i0, j0, k, bar);
             }
         }
+        slab_signal(sched, false);                  // meets the consumer warps at the CTA barrier inside
         return;
     }
 
@@ -346,7 +350,7 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                     res.y = rk_combine_fast<REAL, STAGE>(zc.y, qo.y, Lu.y, a.dt);
                 }
                 *reinterpret_cast<V2*>(po) = res;
-                if (a.out2) *reinterpret_cast<V2*>(a.out2 + (po - out) + a.off2) = res;
+                if (out2) *reinterpret_cast<V2*>(out2 + (po - out) + off2) = res;
             } else {
                 if (yr && zr) {
                     V2 Lu;
@@ -363,7 +367,7 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
                 }
                 if (in_dom) {
                     *reinterpret_cast<V2*>(po) = res;
-                    if (a.out2) *reinterpret_cast<V2*>(a.out2 + (po - out) + a.off2) = res;
+                    if (out2) *reinterpret_cast<V2*>(out2 + (po - out) + off2) = res;
                 }
             }
         }
@@ -386,6 +390,7 @@ heat3d_stage_tma(const __grid_constant__ CUtensorMap tmap, const __grid_constant
         if (!step(q3, q4, q0, q1, q2)) break;
         if (!step(q4, q0, q1, q2, q3)) break;
     }
+    slab_signal(sched, tx == 0 && ty == 0);         // last CTA of a boundary window raises the neighbour's flag
 }
 
 }  // namespace adv
