@@ -1056,8 +1056,11 @@ static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in
 static bool stage_fusable(const adv_solver* s)
 {
     if (env_on("ADV_HALO_MULTILAUNCH") || !get_tmap_encode()) return false;
+    // heat: measured on 2 B200s (tools/r02_ab_fused.sh, profiles/r02_ab_fused_2gpu.log) the one-launch stage is
+    // 0.5 % (512^3 per GPU) to 4.5 % (1024^3 strong) SLOWER than boundary launches + interior launch -- the short
+    // boundary CTAs of the bandwidth-bound kernel do better with the GPU to themselves -- so it is opt-in there
     if (s->d.target == ADV_TARGET_HEAT3D_MGPU)
-        return !env_on("ADV_HEAT_DIRECT") && s->d.nx % 2 == 0 && s->d.nx >= 8;
+        return env_on("ADV_HEAT_ONE_LAUNCH") && !env_on("ADV_HEAT_DIRECT") && s->d.nx % 2 == 0 && s->d.nx >= 8;
     if (s->d.target == ADV_TARGET_BURGERS3D_MGPU)
         return !env_on("ADV_BURGERS_DIRECT") && !env_on("ADV_BURGERS_RING") && s->d.nx >= 8;
     return false;
