@@ -1077,7 +1077,12 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
     if (ob < 0) return fail(ADV_ERR_STATE, "stage output is not one of the solver's buffers");
     const long long plane = (long long)s->pitch * s->urows;
     int rc;
-    if (stage_fusable(s)) {
+    // heat (bandwidth-bound, short stages): both boundary windows, their flag waits and flag releases in ONE launch,
+    // then the interior launch -- 2 launches per stage instead of 2 stream waits + 2 boundary launches + 2 signal
+    // kernels + interior (ADV_HALO_MULTILAUNCH=1 keeps that schedule)
+    const bool two_launch = !stage_fusable(s) && s->d.target == ADV_TARGET_HEAT3D_MGPU && !env_on("ADV_HALO_MULTILAUNCH") &&
+                            !env_on("ADV_HEAT_DIRECT") && get_tmap_encode() && s->d.nx % 2 == 0 && s->d.nx >= 8;
+    if (stage_fusable(s) || two_launch) {
         unsigned* flags = (unsigned*)(s->arena + s->off_flags);
         SlabSched f;
         memset(&f, 0, sizeof(f));
@@ -1101,7 +1106,9 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
         PeerOut po = kNoPeer;
         po.fused = &f;
         const int flo = (r > 0) ? 2 * R : 0, fhi = (r < P - 1) ? s->nzs - 2 * R : s->nzs;
-        return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, po);
+        if (!two_launch) return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, po);
+        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, flo, flo, s->stream, po))) return rc;     // boundary windows only
+        return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, kNoPeer);
     }
     if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1))) return rc;
     if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1))) return rc;
