@@ -1077,10 +1077,12 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
     if (ob < 0) return fail(ADV_ERR_STATE, "stage output is not one of the solver's buffers");
     const long long plane = (long long)s->pitch * s->urows;
     int rc;
-    // heat (bandwidth-bound, short stages): both boundary windows, their flag waits and flag releases in ONE launch,
-    // then the interior launch -- 2 launches per stage instead of 2 stream waits + 2 boundary launches + 2 signal
-    // kernels + interior (ADV_HALO_MULTILAUNCH=1 keeps that schedule)
-    const bool two_launch = !stage_fusable(s) && s->d.target == ADV_TARGET_HEAT3D_MGPU && !env_on("ADV_HALO_MULTILAUNCH") &&
+    // heat, A/B only (ADV_HEAT_TWO_LAUNCH=1): both boundary windows with in-kernel flag wait/release in ONE launch, then
+    // the interior launch.  Measured on 4 B200s (profiles/r02_ab_fused_4gpu.log), 512^3 per GPU: round-1 schedule
+    // (2 stream waits + 2 boundary launches + 2 signal kernels + interior) 1.521 ms per step, everything in one launch
+    // 1.544, this variant 1.575 -- in-kernel flag waits cost the bandwidth-bound kernel more than the launches they
+    // save, so heat keeps the round-1 schedule; Burgers (7.50 -> 7.44 ms) takes the one-launch stage.
+    const bool two_launch = !stage_fusable(s) && s->d.target == ADV_TARGET_HEAT3D_MGPU && env_on("ADV_HEAT_TWO_LAUNCH") &&
                             !env_on("ADV_HEAT_DIRECT") && get_tmap_encode() && s->d.nx % 2 == 0 && s->d.nx >= 8;
     if (stage_fusable(s) || two_launch) {
         unsigned* flags = (unsigned*)(s->arena + s->off_flags);
