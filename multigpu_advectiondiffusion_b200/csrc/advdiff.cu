@@ -196,10 +196,37 @@ static int heat3d_launch_tma(const adv_stage_args* a, const HeatArgs<REAL>& h, c
     if (rc) return rc;
     const int planes = a->k_end - a->k_begin;
     const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + TY - 1) / TY;
+    // z chunks: equal-length CTAs run in waves of (resident CTAs per SM) x (SMs); a launch costs about
+    // waves x (chunk + 4 run-in planes).  Pick the chunk count that minimises that (ADV_HEAT_NCH forces one;
+    // ADV_HEAT_CHUNK_OLD=1 is the round-1 rule: ~2368 CTAs, chunks of >= 16 planes -- 4.6 waves at 256^3).
     const int nch_env = env_int("ADV_HEAT_NCH", 0);
-    int nch = nch_env > 0 ? nch_env : (2368 + gx * gy - 1) / (gx * gy);
+    int nch = (2368 + gx * gy - 1) / (gx * gy);
     if (nch > planes / 16) nch = planes / 16;
     if (nch < 1) nch = 1;
+    if (!env_on("ADV_HEAT_CHUNK_OLD") && planes > 0) {
+        int sms = 148, per_sm = 3, dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        {
+            auto k2 = heat3d_stage_tma<REAL, TY, NST, 2>;
+            if (sizeof(S) > 48 * 1024) cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(S));
+            int occ = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k2, 32 * (TY + 1), sizeof(S)) == cudaSuccess && occ > 0) per_sm = occ;
+        }
+        const long long slots = (long long)sms * per_sm;
+        long long best = -1;
+        // chunks of 16..48 planes (measured at 512^3: 22..44 planes give 96.3-97.0 % of the copy peak, 87 planes
+        // 94.3 %, 14 planes 94.6 %; the 4 run-in planes of a chunk are L2 hits and cost about 2 planes' time);
+        // among those, the count with the fewest waves x (chunk + 2): at 256^3 that is 10 chunks (2.9 waves, 85 %)
+        // where 9 or 11 chunks give 82 % and 80 %
+        for (int c = 1; c <= planes / 16 || c == 1; c++) {
+            const int ch = (planes + c - 1) / c, nz = (planes + ch - 1) / ch;
+            if (ch > 48 && planes / 16 >= 2 && (planes + c) / (c + 1) >= 16) continue;
+            const long long ctas = (long long)gx * gy * nz, waves = (ctas + slots - 1) / slots;
+            const long long cost = waves * (ch + 2);
+            if (best < 0 || cost < best) { best = cost; nch = c; }
+        }
+    }
+    if (nch_env > 0) nch = nch_env;
     const int chunk = planes > 0 ? (planes + nch - 1) / nch : 1;
     const SlabSched sc = make_sched(fused, a->k_begin, a->k_end, chunk);
     dim3 grid(gx, gy, sc.nb + (planes + chunk - 1) / chunk), block(32, TY + 1, 1);
@@ -1281,7 +1308,7 @@ extern "C" int adv_step(adv_solver* s, int nsteps)
     CUDA_TRY(cudaSetDevice(s->d.device));
     const bool no_graph = env_on("ADV_NO_GRAPH");
     const size_t cells = (size_t)s->d.nx * s->urows * s->nzs;
-    const bool use_graph = !no_graph && s->d.nranks == 1 && nsteps >= 12 && cells <= ((size_t)1 << 23);
+    const bool use_graph = !no_graph && s->d.nranks == 1 && nsteps >= 12 && cells <= ((size_t)1 << 25);   // up to 256^3 (65 us heat stages)
     if (use_graph && !s->graph_exec) {
         // capture three steps starting from the current buffer assignment
         cudaGraph_t g = nullptr;
