@@ -11,6 +11,12 @@
 
 #define FLOPS 8.0
 
+/* exit(-1) as the reference does (main.c:14-25), but from whichever thread hits the error: the multi-GPU drivers run
+ * one thread per GPU, and exit() from one of them would run the CUDA runtime's atexit teardown while the sibling
+ * threads are still inside CUDA calls.  _exit leaves at once with the same status (255). */
+#include <unistd.h>
+static void die_now(void) { fflush(stdout); fflush(stderr); _exit(255); }
+
 static double now_s(void)
 {
     struct timespec ts;
@@ -20,7 +26,7 @@ static double now_s(void)
 
 static void die_on(int rc, const char* what)
 {
-    if (rc) { printf("%s: %s\n", what, adv_last_error()); exit(-1); }   /* checkCuda / MPI_CHECK behaviour */
+    if (rc) { printf("%s: %s\n", what, adv_last_error()); die_now(); }   /* checkCuda / MPI_CHECK behaviour: exit(-1) */
 }
 
 /* result.bin / initial.bin: float32 always, headerless, x fastest (one fwrite per element in the

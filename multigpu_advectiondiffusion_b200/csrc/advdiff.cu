@@ -721,8 +721,15 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
     CREATE_TRY(cudaEventCreateWithFlags(&s->ev_comm, cudaEventDisableTiming));
 #undef CREATE_TRY
     if (s->d.nranks > 1) {
-        rc = s->comm.init(s->d.nranks, s->d.rank, s->d.comm_id, g_err, sizeof(g_err));
-        if (rc) { adv_destroy(s); return rc; }
+        // NCCL serves the ncclSend/ncclRecv halo path and the dynamic-CFL all-reduce.  A host without a loadable
+        // libnccl can still run the peer-store halo path: creation succeeds with no communicator, and whatever needs
+        // one later fails with "halo exchange without a communicator" (every rank sees the same missing library).
+        if (!NcclApi::get(g_err, sizeof(g_err))) {
+            s->comm.api = nullptr; s->comm.comm = nullptr; s->comm.nranks = s->d.nranks; s->comm.rank = s->d.rank;
+        } else {
+            rc = s->comm.init(s->d.nranks, s->d.rank, s->d.comm_id, g_err, sizeof(g_err));
+            if (rc) { adv_destroy(s); return rc; }
+        }
     }
     *out = s;
     return ADV_OK;
