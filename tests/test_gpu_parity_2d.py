@@ -45,6 +45,20 @@ def test_heat2d_mgpu_vs_oracle(shape):
     assert rel(got, want) <= TOL64
 
 
+@pytest.mark.parametrize("shape", [(64, 64), (400, 400), (130, 77), (1030, 48)])
+def test_heat2d_tma_row_pipeline_vs_oracle(shape, monkeypatch):
+    """ADV_HEAT2D_TMA=1: the 3-D TMA pipeline applied to a 2-D field seen as nx x 1 x rows.  It is NOT the default:
+    on hardware it holds parity (1.6e-15, not bit-identical to the row kernel: different operand grouping) but reaches
+    only 140 Gcell-updates/s at 8192^2 where heat2d_stage_rows reaches 253 (profiles/r02_heat2d_tma_check.log) -- one
+    consumer warp per 64-column strip leaves too few loads in flight.  Kept tested so that the switch stays usable."""
+    nx, ny = shape
+    monkeypatch.setenv("ADV_HEAT2D_TMA", "1")
+    u0 = orc.ic_heat2d_mgpu(nx, ny) + np.random.default_rng(5).random((ny + 6, nx))
+    want, wi = orc.heat2d_mgpu(u0, 25)
+    got, gi = adv.solve_host("heat2d_mgpu", u0, wi["dt"] * 25, coef=1.0)
+    assert gi["it"] == wi["it"] and rel(got, want) <= TOL64
+
+
 @pytest.mark.parametrize("shape", [(64, 64, 2.0), (400, 400, 2.0), (131, 77, 1.2), (33, 260, 16.0), (1030, 48, 0.1)])
 def test_burgers2d_mgpu_vs_oracle(shape):
     nx, ny, W = shape           # W keeps dy ~ dx so that dt = CFL*dx is stable in y too
