@@ -765,8 +765,11 @@ extern "C" int adv_upload(adv_solver* s, const void* host)
     if (!s || !host) return fail(ADV_ERR_INVALID, "NULL argument");
     CUDA_TRY(cudaSetDevice(s->d.device));
     const size_t row = (size_t)s->d.nx * s->esz;
-    CUDA_TRY(cudaMemcpy2DAsync(s->buf[s->cur], s->pitch * s->esz, host, row, row, (size_t)s->urows * s->nzs,
-                               cudaMemcpyHostToDevice, s->stream));
+    if (s->pitch * s->esz == row)       // rows already start on 128-byte lines: one linear copy
+        CUDA_TRY(cudaMemcpyAsync(s->buf[s->cur], host, row * (size_t)s->urows * s->nzs, cudaMemcpyHostToDevice, s->stream));
+    else
+        CUDA_TRY(cudaMemcpy2DAsync(s->buf[s->cur], s->pitch * s->esz, host, row, row, (size_t)s->urows * s->nzs,
+                                   cudaMemcpyHostToDevice, s->stream));
     s->uploaded = true;
     return ADV_OK;
 }
@@ -777,8 +780,11 @@ extern "C" int adv_download(adv_solver* s, void* host)
     if (!s->uploaded) return fail(ADV_ERR_STATE, "no field uploaded yet");
     CUDA_TRY(cudaSetDevice(s->d.device));
     const size_t row = (size_t)s->d.nx * s->esz;
-    CUDA_TRY(cudaMemcpy2DAsync(host, row, s->buf[s->cur], s->pitch * s->esz, row, (size_t)s->urows * s->nzs,
-                               cudaMemcpyDeviceToHost, s->stream));
+    if (s->pitch * s->esz == row)
+        CUDA_TRY(cudaMemcpyAsync(host, s->buf[s->cur], row * (size_t)s->urows * s->nzs, cudaMemcpyDeviceToHost, s->stream));
+    else
+        CUDA_TRY(cudaMemcpy2DAsync(host, row, s->buf[s->cur], s->pitch * s->esz, row, (size_t)s->urows * s->nzs,
+                                   cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     return ADV_OK;
 }
