@@ -51,6 +51,14 @@ extern "C" const char* adv_last_error(void) { return g_err; }
 
 // A/B switches (ADV_* environment variables) are read at every call, not latched at first use: a caller or a
 // test that sets one after the library has already launched something gets what it asked for.
+// SM count of the current device (148 on B200; queried, not assumed)
+static int current_sm_count()
+{
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms > 0 ? sms : 148;
+}
+
 static bool env_on(const char* name) { return getenv(name) != nullptr; }
 static int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 extern "C" int adv_version(void) { return ADV_VERSION; }
@@ -336,7 +344,7 @@ static int heat2d_stage_impl(const adv_stage_args* a, const REAL* u_in, const RE
     if (vec_ok && (slab || (size_t)a->nx * a->ny > ((size_t)1 << 21))) {
         const int rows = h.ke - h.kb, gx = (a->nx / 2 + 1 + 127) / 128;
         const int ctas_per_sm = env_int("ADV_HEAT2D_CTAS", 128);  // A/B switch; measured at 8192^2: 16 -> 184, 64 -> 239, 128 -> 253 Gcell-updates/s (equal-length CTAs: many waves keep the tail short)
-        int nch = (ctas_per_sm * 148 + gx - 1) / gx;        // many short chunks: loads in flight matter more than the 4 run-in rows ...
+        int nch = (ctas_per_sm * current_sm_count() + gx - 1) / gx;        // many short chunks: loads in flight matter more than the 4 run-in rows ...
         if (nch > rows / 16) nch = rows / 16;               // ... but chunks of >= 16 rows (the 4 run-in rows are L2 hits: neighbouring chunks run together)
         if (nch < 1) nch = 1;
         const int chunk = (rows + nch - 1) / nch;
@@ -448,14 +456,18 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         const int gx = (a->nx + S::TX - 1) / S::TX, gy = (a->ny + S::TY - 1) / S::TY;
         int sms = 148;
         { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        // z chunks: all CTAs take the same time, so the launch runs in waves of 2 CTAs per SM and costs
-        // waves x (chunk + run-in).  Pick the chunk count that minimises that (chunks of >= 12 planes: 5 planes of
-        // staging and one plane of z halves are the run-in, about 3 planes' worth of work).
+        // z chunks: all CTAs take the same time, so the launch runs in waves of 2 CTAs per SM and costs about
+        // waves x (chunk + 3) plane-times (5 planes of staging and one plane of z halves are the run-in).  Measured at
+        // 512^3 (tools/r02_ab_nch.sh): 10-12 chunks (44-52 planes) 7.26 ms per step, 4 chunks (130 planes, the
+        // fewest waves) 7.37, 16 chunks 7.35, 37 chunks (14 planes) 8.02 -- many mid-sized CTAs balance better than the
+        // wave count alone says.  So: chunks of 32..64 planes where the slab allows, and among those the fewest
+        // waves x (chunk + 3).
         const int minchunk = env_int("ADV_BURGERS_MINCHUNK", 12), forced = env_int("ADV_BURGERS_NCH", 0);
         int nch = 1;
         long long best = -1;
         for (int c = 1; c <= planes / minchunk || c == 1; c++) {
             const int ch = (planes + c - 1) / c, nz = (planes + ch - 1) / ch;
+            if (planes >= 64 && (ch > 64 || ch < 32)) continue;
             const long long ctas = (long long)gx * gy * nz, waves = (ctas + 2 * sms - 1) / (2 * sms);
             const long long cost = waves * (ch + 3);
             if (best < 0 || cost < best) { best = cost; nch = c; }
@@ -484,7 +496,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         constexpr int TY = 16, CPT = 2, MINB = 2;
         const int planes = a->k_end - a->k_begin;
         const int gx = (a->nx + 31) / 32, gy = (a->ny + TY - 1) / TY;
-        int nch = (1776 + gx * gy - 1) / (gx * gy);         // ~6 waves of 2 CTAs/SM on 148 SMs ...
+        int nch = (12 * current_sm_count() + gx * gy - 1) / (gx * gy);         // ~6 waves of 2 CTAs/SM ...
         if (nch > planes / 16) nch = planes / 16;           // ... but chunks of >= 16 planes (6 planes of z run-in each)
         if (nch < 1) nch = 1;
         const int chunk = (planes + nch - 1) / nch;
@@ -1401,7 +1413,7 @@ static int run_until_cfl_impl(adv_solver* s, double tEnd_d, int max_steps, doubl
     unsigned long long* d_max = (unsigned long long*)(s->arena + s->off_flags + 256);      // spare words of the flag block
     const REAL tEnd = (REAL)tEnd_d, CFL = (REAL)s->d.coef, dx = (REAL)s->dx;
     const long long rows = (long long)s->urows * s->nzs;
-    const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+    const int grid = (int)(rows < current_sm_count() * 8 ? rows : current_sm_count() * 8);
     REAL dt = 0, it = 0, t = 0;
     while (t < tEnd && (max_steps < 0 || it < max_steps)) {
         CUDA_TRY(cudaMemsetAsync(d_max, 0, sizeof(unsigned long long), s->stream));
@@ -1479,7 +1491,7 @@ static int run_until_cfl_device_impl(adv_solver* s, double tEnd_d, int max_steps
     CUDA_TRY(cudaMemcpyAsync(cs, &h0, sizeof(h0), cudaMemcpyHostToDevice, s->stream));
     // the first step's maximum: one reduction pass over the slab (later ones come out of stage 3)
     const long long rows = (long long)s->urows * s->nzs;
-    const int grid = (int)(rows < 148 * 8 ? rows : 148 * 8);
+    const int grid = (int)(rows < current_sm_count() * 8 ? rows : current_sm_count() * 8);
     absmax_kernel<REAL><<<grid, 256, 0, s->stream>>>((const REAL*)s->buf[s->cur], s->d.nx, (long long)s->pitch, rows, &cs->local_max);
     CUDA_TRY(cudaGetLastError());
     s->launches++;
