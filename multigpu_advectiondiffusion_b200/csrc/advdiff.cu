@@ -675,6 +675,39 @@ static int validate_desc(const adv_desc* d)
     return ADV_OK;
 }
 
+// CUDA loads a kernel's code on its first use (lazy module loading), per device, under a process-wide lock: in the
+// multi-GPU drivers (one thread per GPU) that put tens of milliseconds per rank into the first time step.  Touching
+// the target's stage kernels here moves it into set-up, where the reference's drivers have their own one-time costs.
+template <typename K> static void touch_kernel(K k) { cudaFuncAttributes at; (void)cudaFuncGetAttributes(&at, k); }
+template <typename REAL>
+static void preload_stage_kernels(int target)
+{
+    switch (target) {
+    case ADV_TARGET_BURGERS3D_MGPU:
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 1, false>); touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 2, false>);
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 3, false>); touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 1, true>);
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 2, true>); touch_kernel(burgers3d_stage_pair<REAL, WENO_JS, BMODE_MGPU, 3, true>);
+        break;
+    case ADV_TARGET_BURGERS3D_SGPU:
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 1, false>); touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 2, false>);
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 3, false>);
+        break;
+    case ADV_TARGET_HEAT3D_MGPU: case ADV_TARGET_HEAT3D_SGPU_BASELINE: case ADV_TARGET_HEAT3D_SGPU_BLOCKING:
+        touch_kernel(heat3d_stage_tma<REAL, 8, 6, 1>); touch_kernel(heat3d_stage_tma<REAL, 8, 6, 2>); touch_kernel(heat3d_stage_tma<REAL, 8, 6, 3>);
+        break;
+    case ADV_TARGET_BURGERS2D_MGPU:
+        touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 1, false>); touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 2, false>); touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 3, false>);
+        touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 1, true>); touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 2, true>); touch_kernel(burgers2d_stage_tile<REAL, WENO_JS, 3, true>);
+        break;
+    case ADV_TARGET_HEAT2D_MGPU:
+        touch_kernel(heat2d_stage_rows<REAL, 1, false>); touch_kernel(heat2d_stage_rows<REAL, 2, false>); touch_kernel(heat2d_stage_rows<REAL, 3, false>);
+        touch_kernel(heat2d_stage_rows<REAL, 1, true>); touch_kernel(heat2d_stage_rows<REAL, 2, true>); touch_kernel(heat2d_stage_rows<REAL, 3, true>);
+        break;
+    default: break;
+    }
+    (void)cudaGetLastError();
+}
+
 extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
 {
     if (!out) return fail(ADV_ERR_INVALID, "out is NULL");
@@ -743,6 +776,7 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
             if (rc) { adv_destroy(s); return rc; }
         }
     }
+    if (s->esz == 8) preload_stage_kernels<double>(s->d.target); else preload_stage_kernels<float>(s->d.target);
     *out = s;
     return ADV_OK;
 }

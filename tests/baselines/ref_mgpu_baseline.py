@@ -90,9 +90,9 @@ def main():
                                  "MultiGPU/*_Baseline sources, nvcc -O3 sm_100, MPI calls served by oracle/ref_harness/mpishim"}
     nz = n * P                                              # weak: n^3 per GPU
     case("Burgers3d_Baseline", "ref_Burgers3d_mgpu.run", "Burgers3d_mgpu.run",
-         [0.012, 0.3, 2.0, 2.0, 2.0 * P, n, n, nz, 8, 8, 8], n * n * nz, P, out)
+         [float(os.environ.get("REFMGPU_TEND", "0.05")), 0.3, 2.0, 2.0, 2.0 * P, n, n, nz, 8, 8, 8], n * n * nz, P, out)
     case("Diffusion3d_Baseline", "ref_Diffusion3d_mgpu.run", "Diffusion3d_mgpu.run",
-         [1.0, 2.0, 2.0, 2.0 * P, n, n, nz, 30, 64, 4, 1], n * n * nz, P, out)
+         [1.0, 2.0, 2.0, 2.0 * P, n, n, nz, int(os.environ.get("REFMGPU_ITERS", "200")), 64, 4, 1], n * n * nz, P, out)
     ny = n2 * P
     case("Burgers2d_Baseline", "ref_Burgers2d_mgpu.run", "Burgers2d_mgpu.run",
          [0.01, 0.4, 2.0, 2.0 * P, n2, ny, 32, 32], n2 * ny, P, out)
