@@ -202,6 +202,11 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         s.upload(u)
         s.step(nsteps)
         u_again = s.download()
+        # the timed exchange on its own (adv_halo_probe) re-sends the boundary planes that are already in the
+        # neighbours' ghost planes: it must leave the field as it is
+        ms, sent = s.halo_probe(3)
+        assert ms > 0 and sent > 0
+        assert np.array_equal(s.download(), u_again), "rank %d: adv_halo_probe changed the field" % rank
     parts = [None] * P if rank == 0 else None
     dist.gather_object(u, parts, dst=0)
     parts_again = [None] * P if rank == 0 else None

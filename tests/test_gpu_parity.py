@@ -331,3 +331,23 @@ def test_dynamic_cfl_time_step_vs_oracle(monkeypatch):
         h.upload(u0)
         with pytest.raises(adv.AdvError):
             h.run_until_cfl(0.01)
+
+
+@pytest.mark.parametrize("target,shape", [("burgers3d_mgpu", (40, 36, 32)), ("burgers3d_sgpu", (40, 36, 32)), ("heat3d_mgpu", (40, 36, 32)),
+                                          ("heat3d_sgpu_baseline", (40, 36, 32)), ("heat2d_sgpu", (64, 48, 1)),
+                                          ("burgers2d_mgpu", (72, 96, 1)), ("heat2d_mgpu", (70, 96, 1))])
+def test_device_side_initial_condition_matches_the_host_generator(target, shape):
+    """adv_init_reference_ic_device: the reference's closed forms evaluated by a kernel.  The device's exp()
+    is not the host libm's, so Gaussians agree to a few ulp (asserted: 1e-15 of the peak value 1), and the piecewise
+    constant heat ICs (square pulse, disc) exactly."""
+    nx, ny, nz = shape
+    with adv.Solver(target, nx, ny, nz, coef=0.3 if "burgers" in target else 1.0) as s:
+        s.init_reference_ic()
+        host = s.download()
+        s.init_reference_ic_device()
+        dev = s.download()
+    if target in ("heat3d_mgpu", "heat2d_mgpu"):
+        assert np.array_equal(host, dev)
+    else:
+        assert np.abs(host - dev).max() <= 1e-15
+        assert np.abs(host).max() > 0.5
