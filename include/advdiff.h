@@ -64,7 +64,11 @@ enum {
     /* MultiGPU/Diffusion3d_Baseline: z-padded, kx/12-isotropic operator (Kernels.cu:240-243),
      * dt factor 0.8, RK on x,y in [3,N-4] for every stored plane */
     ADV_TARGET_HEAT3D_MGPU = 3,
-    /* SingleGPU/Burgers3d_WENO5: WENO5-Z + C=1e-5 viscous term, frame of 3 frozen */
+    /* SingleGPU/Burgers3d_WENO5: WENO5-Z + C=1e-5 viscous term, frame of 3 frozen.  Also accepted with
+     * nranks > 1 (no counterpart in the reference, whose multi-GPU Burgers program is the JS/inviscid one below):
+     * the same semantics on z-slabs -- the frozen frame planes 0..2 and nz-3..nz-1 stand in for pad planes, rank r
+     * owns global planes [3 + r*m, 3 + (r+1)*m), m = (nz-6)/nranks, and stores m + 6 planes; results equal the
+     * one-rank run bit for bit */
     ADV_TARGET_BURGERS3D_SGPU = 4,
     /* MultiGPU/Burgers3d_Baseline: WENO5-JS inviscid, z-padded, RK on every cell, the
      * i=2 / j=2 pseudo-updates of the reference at np>=2 */
@@ -146,8 +150,10 @@ int  adv_step(adv_solver* s, int nsteps);
 int  adv_run_until(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached);
 /* SURVEY 8f-2, no counterpart in the reference's CUDA programs: the same loop with the time step of its Matlab
  * prototype, dt = CFL*dx/max|u| recomputed before every step (LFWENO5FDM3d.m:71) instead of the drivers'
- * max|u| = 1 (main.c:193); max over every stored cell of the slab, one reduction pass + one 8-byte device-to-host
- * read per step.  Burgers targets, single rank (nranks == 1) for now. */
+ * max|u| = 1 (main.c:193); max over every stored cell of every rank.  3-D Burgers targets: everything on the
+ * device (max|u| folded into stage 3, one 8-byte all-reduce across ranks, dt computed by a kernel, no host
+ * synchronisation in the loop), any nranks -- call it on every rank; all ranks return the same dt, step count and
+ * time.  2-D Burgers target: one reduction pass + one 8-byte device-to-host read per step, nranks == 1. */
 int  adv_run_until_cfl(adv_solver* s, double tEnd, int max_steps, double* dt_last, double* steps, double* t_reached);
 int  adv_sync(adv_solver* s);
 /* device time (ms) spent in the last adv_step/adv_run_until call, measured with CUDA events on

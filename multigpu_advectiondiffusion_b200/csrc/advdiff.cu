@@ -88,6 +88,12 @@ static bool is_heat(int t)
 // the two y-slab programs: the slab unit is one ROW (pitch elements), not one z-plane
 static bool is_2d_mgpu(int t) { return t == ADV_TARGET_HEAT2D_MGPU || t == ADV_TARGET_BURGERS2D_MGPU; }
 static bool is_mgpu(int t) { return t == ADV_TARGET_HEAT3D_MGPU || t == ADV_TARGET_BURGERS3D_MGPU || is_2d_mgpu(t); }
+// SURVEY 8f-4 tail: the single-GPU Burgers program (WENO5-Z + viscous term, frozen frame of 3) on z-slabs.  Its array
+// has no pad planes, but its frame planes 0..2 and nz-3..nz-1 are never updated, so they play the pads' part: rank r of
+// P owns global planes [3 + r*m, 3 + (r+1)*m), m = (nz-6)/P, and stores planes [r*m, r*m + m + 6) -- the layout of the
+// MGPU targets with nz-6 "physical" planes.  Parity target: the single-GPU program's own semantics, which the slab
+// run reproduces bit for bit for every P (tests/mp_slab_worker.py).
+static bool is_sgpu_slab(const adv_desc& d) { return d.target == ADV_TARGET_BURGERS3D_SGPU && d.nranks > 1; }
 
 // second destination of a stage launch (fused halo exchange); internal, not part of the public stage ABI
 struct PeerOut {
@@ -446,6 +452,7 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
     // default: the pair kernel (TMA-staged planes; needs 16-byte rows for the tensor map)
     const bool pair_ok = !force_direct && !env_on("ADV_BURGERS_RING") && get_tmap_encode() != nullptr &&
                          ((uintptr_t)u_in % 16 == 0) && ((a->pitch * sizeof(REAL)) % 16 == 0) && a->nx >= 8;
+    if (!mg && peer.out2 && !pair_ok) return fail(ADV_ERR_STATE, "peer-store halos of the single-GPU Burgers semantics need the pair kernel");
     if ((peer.cfl_done || peer.fused) && !pair_ok) return fail(ADV_ERR_STATE, "the device-resident time step and the one-launch stage need the pair kernel");
     if (pair_ok) {
         typedef BurgersPairSmem<REAL> S;
@@ -486,7 +493,8 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
             if (a->stage == 1) LAUNCH_PAIR(W_, M_, 1, PEER_); \
             else if (a->stage == 2) LAUNCH_PAIR(W_, M_, 2, PEER_); \
             else LAUNCH_PAIR(W_, M_, 3, PEER_); } while (0)
-        if (!mg) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, false);
+        if (!mg && (b.out2 || peer.fused)) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, true);
+        else if (!mg) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, false);
         else if (b.out2 || peer.fused) LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, true);
         else LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, false);
 #undef LAUNCH_PAIR_S
@@ -662,8 +670,12 @@ static int validate_desc(const adv_desc* d)
     const bool two_d = d->target == ADV_TARGET_HEAT2D_SGPU || is_2d_mgpu(d->target);
     if (!two_d && d->nz < minn) return fail(ADV_ERR_INVALID, "grid too small: nz=%d", d->nz);
     const int P = d->nranks <= 0 ? 1 : d->nranks;
-    if (P > 1 && !is_mgpu(d->target)) return fail(ADV_ERR_INVALID, "slab decomposition needs an MGPU target");
-    if (P > 1) {
+    if (P > 1 && d->target == ADV_TARGET_BURGERS3D_SGPU) {
+        if (d->rank < 0 || d->rank >= P) return fail(ADV_ERR_INVALID, "rank %d outside [0,%d)", d->rank, P);
+        if ((d->nz - 2 * ADV_RADIUS) % P) return fail(ADV_ERR_INVALID, "nz-6=%d interior planes are not divisible by nranks=%d", d->nz - 2 * ADV_RADIUS, P);
+        if ((d->nz - 2 * ADV_RADIUS) / P < 2 * ADV_RADIUS) return fail(ADV_ERR_INVALID, "slab of %d planes is thinner than 2*RADIUS", (d->nz - 2 * ADV_RADIUS) / P);
+    } else if (P > 1 && !is_mgpu(d->target)) return fail(ADV_ERR_INVALID, "slab decomposition needs an MGPU target (or ADV_TARGET_BURGERS3D_SGPU)");
+    if (P > 1 && is_mgpu(d->target)) {
         if (d->rank < 0 || d->rank >= P) return fail(ADV_ERR_INVALID, "rank %d outside [0,%d)", d->rank, P);
         // the reference silently drops planes (rows) when Nz %% P != 0 (main.c:64); refuse instead
         const int n = is_2d_mgpu(d->target) ? d->ny : d->nz;
@@ -691,6 +703,8 @@ static void preload_stage_kernels(int target)
     case ADV_TARGET_BURGERS3D_SGPU:
         touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 1, false>); touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 2, false>);
         touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 3, false>);
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 1, true>); touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 2, true>);
+        touch_kernel(burgers3d_stage_pair<REAL, WENO_Z, BMODE_SGPU, 3, true>);
         break;
     case ADV_TARGET_HEAT3D_MGPU: case ADV_TARGET_HEAT3D_SGPU_BASELINE: case ADV_TARGET_HEAT3D_SGPU_BLOCKING:
         touch_kernel(heat3d_stage_tma<REAL, 8, 6, 1>); touch_kernel(heat3d_stage_tma<REAL, 8, 6, 2>); touch_kernel(heat3d_stage_tma<REAL, 8, 6, 3>);
@@ -732,8 +746,9 @@ extern "C" int adv_create(const adv_desc* desc, adv_solver** out)
     s->esz = desc->precision == ADV_F64 ? 8 : 4;
     s->urows = is_2d_mgpu(s->d.target) ? 1 : s->d.ny;
     s->nsplit = is_2d_mgpu(s->d.target) ? s->d.ny : s->d.nz;
+    if (is_sgpu_slab(s->d)) s->nsplit = s->d.nz - 2 * ADV_RADIUS;
     s->nzl = s->nsplit / s->d.nranks;
-    s->nzs = is_mgpu(desc->target) ? s->nzl + 2 * ADV_RADIUS : s->nzl;
+    s->nzs = (is_mgpu(desc->target) || is_sgpu_slab(s->d)) ? s->nzl + 2 * ADV_RADIUS : s->nzl;
     const size_t align = 128 / s->esz;                  // rows start on 128-byte lines
     s->pitch = ((size_t)desc->nx + align - 1) / align * align;
     s->buf_bytes = s->pitch * (size_t)s->urows * (size_t)s->nzs * s->esz;
@@ -870,7 +885,7 @@ static void reference_ic_local(const adv_solver* s, REAL* h)
     const int nx = d.nx, ny = s->urows;                                  // y-slab targets: one row per slab unit, k = global row
     const REAL dx = (REAL)s->dx, dy = (REAL)s->dy, dz = (REAL)s->dz;
     const int NZ = is_mgpu(d.target) ? s->nsplit + 2 * ADV_RADIUS : d.nz; // global stored planes (rows)
-    const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;            // Init_subdomain, Tools.c:181-200
+    const int kg0 = (is_mgpu(d.target) || is_sgpu_slab(d)) ? d.rank * s->nzl : 0;            // Init_subdomain, Tools.c:181-200
     // every value depends on its own indices only: slab units are spread over host threads (same libm calls,
     // same bits; at 512^3 the serial loop was the longest part of a driver's set-up)
     const int units = s->nzs;
@@ -1006,7 +1021,7 @@ extern "C" int adv_init_reference_ic_device(adv_solver* s)
     CUDA_TRY(cudaSetDevice(s->d.device));
     const adv_desc& d = s->d;
     const int NZ = is_mgpu(d.target) ? s->nsplit + 2 * ADV_RADIUS : d.nz;
-    const int kg0 = is_mgpu(d.target) ? d.rank * s->nzl : 0;
+    const int kg0 = (is_mgpu(d.target) || is_sgpu_slab(d)) ? d.rank * s->nzl : 0;
     dim3 block(256, 1, 1), grid((d.nx + 255) / 256, s->urows, s->nzs < 1024 ? s->nzs : 1024);
     if (s->esz == 8)
         reference_ic_kernel<double><<<grid, block, 0, s->stream>>>((double*)s->buf[s->cur], d.target, d.nx, s->urows, s->nzs,
@@ -1039,7 +1054,7 @@ static int launch_stage_peer(adv_solver* s, int stage, double dt, const void* in
     a.k_begin = kb; a.k_end = ke;
     a.own_lo = is_mgpu(s->d.target) ? ADV_RADIUS : 3;
     a.own_hi = s->nzs - 3;
-    a.k_global0 = yslab ? s->d.rank * s->nzl : 0;
+    a.k_global0 = (yslab || is_sgpu_slab(s->d)) ? s->d.rank * s->nzl : 0;
     a.dt = dt; a.dx = s->dx; a.dy = s->dy; a.dz = s->dz; a.kx = s->kx; a.ky = s->ky; a.kz = s->kz;
     int rc;
     const bool f64 = s->esz == 8;
@@ -1147,7 +1162,7 @@ static bool stage_fusable(const adv_solver* s)
     // boundary CTAs of the bandwidth-bound kernel do better with the GPU to themselves -- so it is opt-in there
     if (s->d.target == ADV_TARGET_HEAT3D_MGPU)
         return env_on("ADV_HEAT_ONE_LAUNCH") && !env_on("ADV_HEAT_DIRECT") && s->d.nx % 2 == 0 && s->d.nx >= 8;
-    if (s->d.target == ADV_TARGET_BURGERS3D_MGPU)
+    if (s->d.target == ADV_TARGET_BURGERS3D_MGPU || s->d.target == ADV_TARGET_BURGERS3D_SGPU)
         return !env_on("ADV_BURGERS_DIRECT") && !env_on("ADV_BURGERS_RING") && s->d.nx >= 8;
     return false;
 }

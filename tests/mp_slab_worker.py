@@ -179,10 +179,14 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
     if two_d:       # y-slabs: the split axis is y, arrays are (ny+6, nx)
         g = orc.ic_burgers2d_mgpu(nx, ny) if "burgers" in target else orc.ic_heat2d_mgpu(nx, ny)
         nz = ny
+    elif target == "burgers3d_sgpu":
+        # SingleGPU/Burgers3d_WENO5 semantics (WENO5-Z + viscous term, frozen frame) on slabs: the program's array has
+        # nz + 6 planes of which the outer 3 + 3 are its frozen frame -- they take the place of the pad planes
+        g = orc.ic_burgers3d_sgpu(nx, ny, nz + 6)
     else:
         g = orc.ic_burgers3d_mgpu(nx, ny, nz) if "burgers" in target else orc.ic_heat3d_mgpu(nx, ny, nz)
     g0, g1 = slab_bounds(nz, P, rank)
-    nz_arg = 1 if two_d else nz
+    nz_arg = 1 if two_d else (nz + 6 if target == "burgers3d_sgpu" else nz)
     with adv.Solver(target, nx, ny, nz_arg, coef=coef, device=rank, nranks=P, rank=rank, comm_id=idb[0]) as s:
         if halo == "peer":
             hs = [None] * P
@@ -233,6 +237,8 @@ def run_gpu(rank, P, target, nx, ny, nz, nsteps, halo="nccl"):
         elif target == "heat2d_mgpu":
             want, wi = orc.heat2d_mgpu(g, nsteps)
             assert wi["it"] == nsteps
+        elif target == "burgers3d_sgpu":
+            want, _ = orc.burgers3d_sgpu(g, 1e9, max_steps=nsteps)
         elif "burgers" in target:
             want, _ = orc.burgers3d_mgpu(g, 1e9, max_steps=nsteps)
         else:
@@ -298,7 +304,7 @@ def main():
             run_cpu_heat2d(rank, P, 34, 48, 4)
         else:
             for halo in ("nccl", "peer"):
-                for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5),
+                for target, shape, steps in (("burgers3d_mgpu", (40, 36, 48), 3), ("burgers3d_sgpu", (40, 36, 48), 3), ("heat3d_mgpu", (64, 40, 48), 5),
                                              ("burgers2d_mgpu", (72, 96, 1), 3), ("heat2d_mgpu", (70, 96, 1), 5)):
                     run_gpu(rank, P, target, *shape, steps, halo=halo)
                 run_gpu_cfl(rank, P, 40, 36, 48, 0.15, halo)

@@ -35,7 +35,7 @@ def test_gpu_nccl_two_ranks():
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
     r = _launch("gpu", 2, 29733)
     print("".join(ln + "\n" for ln in r.stdout.splitlines() if ln.startswith("MP_OK")))      # kept in the log with pytest -s
-    assert r.returncode == 0 and r.stdout.count("MP_OK gpu ") == 8 and r.stdout.count("MP_OK gpu_cfl") == 2 and r.stdout.count("halo=peer") == 5, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu ") == 10 and r.stdout.count("MP_OK gpu_cfl") == 2 and r.stdout.count("halo=peer") == 6, r.stdout[-3000:] + r.stderr[-3000:]
 
 
 @pytest.mark.gpu
@@ -46,4 +46,4 @@ def test_gpu_four_ranks_both_halo_modes():
         pytest.skip("needs 4 GPUs (run under gpurun --gpus 4)")
     r = _launch("gpu", 4, 29734)
     print("".join(ln + "\n" for ln in r.stdout.splitlines() if ln.startswith("MP_OK")))
-    assert r.returncode == 0 and r.stdout.count("MP_OK gpu ") == 8 and r.stdout.count("MP_OK gpu_cfl") == 2 and r.stdout.count("halo=peer") == 5, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.returncode == 0 and r.stdout.count("MP_OK gpu ") == 10 and r.stdout.count("MP_OK gpu_cfl") == 2 and r.stdout.count("halo=peer") == 6, r.stdout[-3000:] + r.stderr[-3000:]
