@@ -105,8 +105,8 @@ def measured_peak():
 
 def ncu_profile(workload):
     """Per-launch numbers of the dominant kernel from the committed ncu --set full capture (profiles/traffic.json,
-    written by tools/ncu_traffic.py).  A capture describes ONE build of the kernel: it records the hash of that
-    kernel family's SASS, and is used only while the built library still carries the same hash
+    written by tools/ncu_traffic.py).  A capture describes ONE build of the kernel: it records the hash of the SASS of
+    the instantiations it profiled (a regular expression over their mangled names), and is used only while the built library still carries the same hash
     (multigpu_advectiondiffusion_b200/kernel_hashes.json, written by the Makefile) -- otherwise the instruction
     counts and DRAM bytes would silently describe a kernel that no longer exists."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -124,7 +124,8 @@ def ncu_profile(workload):
     try:
         import hashlib
         built = json.load(open(os.path.join(ROOT, "multigpu_advectiondiffusion_b200", "kernel_hashes.json")))
-        items = sorted((k, v) for k, v in built.items() if fam and fam in k)       # = tools/sass_hashes.py family_hash
+        import re
+        items = sorted((k, v) for k, v in built.items() if fam and re.search(fam, k))  # = tools/sass_hashes.py family_hash
         have = hashlib.md5(json.dumps(items).encode()).hexdigest() if items else None
     except Exception:
         pass

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Writes one workload's entry of profiles/traffic.json from an `ncu --set full` capture of bench.py:
 
-    python tools/ncu_traffic.py <workload> <kernel family> <rep.ncu-rep> [first launch index]
+    python tools/ncu_traffic.py <workload> <kernel name> <rep.ncu-rep> <regex over mangled names of the captured instantiations> [first launch index]
 
 The three launches starting at the index (default 0) must be stages 1, 2, 3 of one time step of the dominant
 kernel.  Recorded per launch: DRAM bytes read + written, executed warp instructions, FP64 pipe activity and
@@ -22,8 +22,8 @@ from sass_hashes import family_hash, hashes  # noqa: E402
 
 
 def main():
-    workload, family, rep = sys.argv[1:4]
-    first = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+    workload, family, rep, mangled_re = sys.argv[1:5]
+    first = int(sys.argv[5]) if len(sys.argv) > 5 else 0
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, data = rows[0], rows[1], rows[2:]
@@ -65,8 +65,8 @@ def main():
         "fp64_share_of_inst_stage2": fp64 / tot if tot else None,
         "fp64_pipe_active_pct_stage123": col("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
         "ncu_duration_s_stage123": dur,
-        "kernel_family": family,
-        "sass_md5": family_hash(hashes(), family),
+        "kernel_family": mangled_re,
+        "sass_md5": family_hash(hashes(), mangled_re),
         "source": "%s (ncu --set full --clock-control none; 3 consecutive launches = stages 1,2,3 of one time step; FP64 share from the source page of the first captured launch)" % os.path.relpath(rep, ROOT),
     }
     p = os.path.join(ROOT, "profiles", "traffic.json")

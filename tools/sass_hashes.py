@@ -26,8 +26,10 @@ def hashes():
 
 
 def family_hash(hashes_by_kernel, family):
-    """one hash for all instantiations of a kernel template (mangled names containing `family`)"""
-    items = sorted((k, v) for k, v in hashes_by_kernel.items() if family in k)
+    """one hash for the instantiations of a kernel template whose mangled names match the regular expression `family`
+    (the ones a capture actually profiled, e.g. r"burgers3d_stage_pairIdLi0ELi1ELi[123]ELb0E": double, WENO5-JS,
+    multi-GPU semantics, stages 1-3, no peer store) -- adding other instantiations to the library leaves it alone"""
+    items = sorted((k, v) for k, v in hashes_by_kernel.items() if re.search(family, k))
     return hashlib.md5(json.dumps(items).encode()).hexdigest() if items else None
 
 
