@@ -85,9 +85,16 @@ burgers2d_stage_tile(BurgersArgs<REAL> a, const REAL* __restrict__ u, const REAL
         return f;
     };
     // face at (cell m) + 1/2 along a line of the (f+, f-) tile with element stride s; q points at cell m
+    // round 2: the 40-instruction side of the 3-D pair kernel (weno_core6: forward differences, halved P_0, one cubic
+    // reciprocal step) instead of weno_side6 (43)
+    const REAL* __restrict__ we = (W == WENO_JS) ? a.wp : a.wc;
     auto face6 = [&](const V2* q, int s) -> REAL {
         const V2 qa = q[-2 * s], qb = q[-s], qc = q[0], qd = q[s], qe = q[2 * s], qf = q[3 * s];
-        return weno_side6<REAL, W>(qa.x, qb.x, qc.x, qd.x, qe.x, wc) + weno_side6<REAL, W>(qf.y, qe.y, qd.y, qc.y, qb.y, wc);
+        const REAL g0 = qb.x - qa.x, g1 = qc.x - qb.x, g2 = qd.x - qc.x, g3 = qe.x - qd.x;
+        const REAL hn = weno_core6<REAL, W, false>(qc.x, g0, g1, g2, g3, g1 - g0, g2 - g1, g3 - g2, we, wc);      // centred on c, from f+
+        const REAL h0 = qc.y - qb.y, h1 = qd.y - qc.y, h2 = qe.y - qd.y, h3 = qf.y - qe.y;
+        const REAL hp = weno_core6<REAL, W, true>(qd.y, h0, h1, h2, h3, h1 - h0, h2 - h1, h3 - h2, we, wc);       // centred on d, from f-, read backwards
+        return hn + hp;
     };
 
     // (1) own cells (kept in registers), then the halo frame; points outside the array are zero

@@ -276,6 +276,58 @@ __device__ __forceinline__ REAL weno_side6(REAL a, REAL b, REAL c, REAL d, REAL 
     }
 }
 
+// reciprocal from the hardware seed (rcp.approx.ftz.f64, ~2^-23) and ONE cubic correction step:
+// y = y0 (1 + e + e^2), e = 1 - den*y0  ->  relative error e^3 plus rounding; three FMAs instead of the four of two
+// Newton steps
+__device__ __forceinline__ double fast_rcp3(double den)
+{
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(den));
+    const double e = fma(-den, y, 1.0);
+    const double r = fma(e, e, e);
+    return fma(y, r, y);
+}
+__device__ __forceinline__ float fast_rcp3(float den) { return __frcp_rn(den); }
+
+// SIX TIMES the one-sided WENO5 value centred on c, from the FORWARD differences along the line
+//   g0 = b-a, g1 = c-b, g2 = d-c, g3 = e-d   and   t_k = g_{k+1} - g_k   of the five values (a, b, c, d, e).
+// REV = false: the value weno_side6(a, b, c, d, e) stands for; REV = true: weno_side6(e, d, c, b, a) -- the same
+// differences read backwards (signs folded into the FMAs), so a cell's minus- and plus-side halves and the halves
+// of the next cell along the line share their differences.  Same formulas as weno_side6, 40 FP64 instructions
+// instead of 43: differences of differences (14 -> 13), the halved P_0 (see BurgersArgs::wp), one cubic
+// reciprocal step.  `we` = BurgersArgs::wp (JS) or ::wc (Z).
+template <typename REAL, int W, bool REV>
+__device__ __forceinline__ REAL weno_core6(REAL c, REAL g0, REAL g1, REAL g2, REAL g3, REAL t0, REAL t1, REAL t2,
+                                           const REAL* __restrict__ we, const REAL* __restrict__ wc)
+{
+    const REAL T0 = REV ? t2 : t0, T2 = REV ? t0 : t2;
+    const REAL sa = fma(REAL(2), g1, t0);       // a - 4b + 3c
+    const REAL sb = fma(REAL(-2), g2, t2);      // 3c - 4d + e
+    const REAL S0 = REV ? sb : sa, S2 = REV ? sa : sb;
+    const REAL S1 = g1 + g2;                    // d - b (enters squared)
+    const REAL q6 = REV ? fma(REAL(6), c, -fma(REAL(2), g1, g2)) : fma(REAL(6), c, fma(REAL(2), g2, g1));
+    (void)g0; (void)g3;
+    const REAL E0 = (we[0] * T0) * T0 + ((we[3] * S0) * S0 + we[6]);
+    const REAL E1 = (we[1] * t1) * t1 + ((we[4] * S1) * S1 + we[7]);
+    const REAL E2 = (we[2] * T2) * T2 + ((we[5] * S2) * S2 + we[8]);
+    const REAL d01 = T0 - t1, d12 = t1 - T2;
+    if (W == WENO_JS) {
+        const REAL P0 = E0 * E0, P1 = E1 * E1, P2 = E2 * E2;      // P0 is half its textbook value
+        const REAL n0 = P1 * P2, n1 = P0 * P2, n2 = P0 * P1;
+        const REAL num = fma(d12, n2, d01 * n0);
+        const REAL den = fma(REAL(0.5), n0, n1 + n2);
+        return fma(num, fast_rcp3(den), q6);
+    } else {
+        const REAL tau = fabs(E0 - E2);
+        const REAL A0 = (wc[16] * (E0 + tau)) * (E1 * E2);
+        const REAL A1 = (wc[17] * (E1 + tau)) * (E0 * E2);
+        const REAL A2 = (wc[18] * (E2 + tau)) * (E0 * E1);
+        const REAL A = d01 * A0;
+        const REAL num = fma(d12, A2, A + A);
+        return fma(num, fast_rcp3((A0 + A1) + A2), q6);
+    }
+}
+
 template <typename REAL> __device__ __forceinline__ bool is_neg(REAL v);
 template <> __device__ __forceinline__ bool is_neg<double>(double v) { return __double2hiint(v) < 0; }
 template <> __device__ __forceinline__ bool is_neg<float>(float v) { return __float_as_int(v) < 0; }
