@@ -485,14 +485,15 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         dim3 pgrid(gx, gy, sc.nb + (planes + chunk - 1) / chunk), pblock(32, S::NW, 1);
         const REAL* uo_ = a->stage == 1 ? u_in : uo;
         const size_t shm = sizeof(S);
-#define LAUNCH_PAIR(W_, M_, STAGE_, PEER_) do { \
-            auto kfn = burgers3d_stage_pair<REAL, W_, M_, STAGE_, PEER_>; \
+#define LAUNCH_PAIR(W_, M_, STAGE_, PEER_, TRACK_) do { \
+            auto kfn = burgers3d_stage_pair<REAL, W_, M_, STAGE_, PEER_, TRACK_>; \
             CUDA_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shm)); \
             kfn<<<pgrid, pblock, shm, st>>>(tm, b, sc, u_in, uo_, u_out, rowacc); } while (0)
 #define LAUNCH_PAIR_S(W_, M_, PEER_) do { \
-            if (a->stage == 1) LAUNCH_PAIR(W_, M_, 1, PEER_); \
-            else if (a->stage == 2) LAUNCH_PAIR(W_, M_, 2, PEER_); \
-            else LAUNCH_PAIR(W_, M_, 3, PEER_); } while (0)
+            if (a->stage == 1) LAUNCH_PAIR(W_, M_, 1, PEER_, false); \
+            else if (a->stage == 2) LAUNCH_PAIR(W_, M_, 2, PEER_, false); \
+            else if (b.cfl_umax) LAUNCH_PAIR(W_, M_, 3, PEER_, true);   /* stage 3 of a dynamic CFL run also tracks max|u| */ \
+            else LAUNCH_PAIR(W_, M_, 3, PEER_, false); } while (0)
         if (!mg && (b.out2 || peer.fused)) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, true);
         else if (!mg) LAUNCH_PAIR_S(WENO_Z, BMODE_SGPU, false);
         else if (b.out2 || peer.fused) LAUNCH_PAIR_S(WENO_JS, BMODE_MGPU, true);

@@ -56,7 +56,9 @@ struct BurgersPairSmem {
     static constexpr int NLAND = (2 * RAWB <= (int)sizeof(Slot)) ? 5 : 4;
 };
 
-template <typename REAL, int W, int MODE, int STAGE, bool PEER>
+// TRACK: fold max|u_out| into *a.cfl_umax (stage 3 of a dynamic CFL run); a separate instantiation so that the
+// fixed-dt stage 3 carries none of it
+template <typename REAL, int W, int MODE, int STAGE, bool PEER, bool TRACK = false>
 __global__ void __launch_bounds__(256, 2)
 burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL> a, SlabSched sched,
                      const REAL* __restrict__ u, const REAL* __restrict__ uo, REAL* __restrict__ out, REAL* __restrict__ rowacc)
@@ -79,7 +81,7 @@ burgers3d_stage_pair(const __grid_constant__ CUtensorMap tmap, BurgersArgs<REAL>
         slab_signal(sched, threadIdx.x == 0 && threadIdx.y == 0);   // but keeps the neighbours' stage counters moving
         return;
     }
-    const bool track = (STAGE == 3) && a.cfl_umax != nullptr;
+    constexpr bool track = TRACK;
     unsigned long long umax_bits = 0;       // max |value stored| by this thread (stage 3 of a dynamic CFL run)
     const long long P = a.pitch, Z = a.plane;
     const REAL* __restrict__ wc = a.wc;

@@ -17,7 +17,7 @@ timeout -s KILL 200 ncu --metrics gpu__time_duration.sum --clock-control none -c
 timeout -s KILL 300 ncu --set full --clock-control none --import-source on --kernel-name regex:burgers3d_stage_pair --launch-skip 9 --launch-count 3 -o $out/pair_512 -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-also --no-e2e > $out/ncu_pair.log 2>&1; echo "ncu rc=$?"
 # the reports are ~45 MB each and gpurun brings back at most 64 MiB: summarise on the box, keep the text
 python tools/ncu_summary.py $out/pair_512.ncu-rep 1 > $out/burgers_pair_512_ncu.txt 2>&1
-python tools/ncu_traffic.py burgers3d_weak512 burgers3d_stage_pair $out/pair_512.ncu-rep 'burgers3d_stage_pairIdLi0ELi1ELi[123]ELb0E' > $out/traffic_burgers.log 2>&1
+python tools/ncu_traffic.py burgers3d_weak512 burgers3d_stage_pair $out/pair_512.ncu-rep 'burgers3d_stage_pairIdLi0ELi1ELi[123]ELb0ELb0E' > $out/traffic_burgers.log 2>&1
 rm -f $out/pair_512.ncu-rep
 timeout -s KILL 200 ncu --set full --clock-control none --import-source on --kernel-name regex:heat3d_stage_tma --launch-skip 9 --launch-count 3 -o $out/heat_512 -f python bench.py --workload heat3d_weak512 --steps 2 --warmup 3 --no-cpu-baseline --no-also --no-e2e > $out/ncu_heat.log 2>&1; echo "ncu heat rc=$?"
 python tools/ncu_summary.py $out/heat_512.ncu-rep 1 > $out/heat_tma_512_ncu.txt 2>&1
