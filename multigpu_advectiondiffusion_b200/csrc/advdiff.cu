@@ -467,16 +467,17 @@ static int burgers3d_stage_impl(const adv_stage_args* a, const REAL* u_in, const
         // waves x (chunk + 3) plane-times (5 planes of staging and one plane of z halves are the run-in).  Measured at
         // 512^3 (tools/r02_ab_nch.sh): 10-12 chunks (44-52 planes) 7.26 ms per step, 4 chunks (130 planes, the
         // fewest waves) 7.37, 16 chunks 7.35, 37 chunks (14 planes) 8.02 -- many mid-sized CTAs balance better than the
-        // wave count alone says.  So: chunks of 32..64 planes where the slab allows, and among those the fewest
-        // waves x (chunk + 3).
+        // wave count alone says.  So: chunks of 16..64 planes where the slab allows, and among those the fewest
+        // waves x (chunk + 4): 9 chunks of 58 planes at 512^3 (7.19 ms), 9 chunks of 30 planes at 256^3 (four full waves;
+        // a 32-plane floor picked 6 chunks = 2.6 waves there and lost 6 %).
         const int minchunk = env_int("ADV_BURGERS_MINCHUNK", 12), forced = env_int("ADV_BURGERS_NCH", 0);
         int nch = 1;
         long long best = -1;
         for (int c = 1; c <= planes / minchunk || c == 1; c++) {
             const int ch = (planes + c - 1) / c, nz = (planes + ch - 1) / ch;
-            if (planes >= 64 && (ch > 64 || ch < 32)) continue;
+            if (planes >= 64 && (ch > 64 || ch < 16)) continue;
             const long long ctas = (long long)gx * gy * nz, waves = (ctas + 2 * sms - 1) / (2 * sms);
-            const long long cost = waves * (ch + 3);
+            const long long cost = waves * (ch + 4);
             if (best < 0 || cost < best) { best = cost; nch = c; }
         }
         if (forced > 0) nch = forced;
