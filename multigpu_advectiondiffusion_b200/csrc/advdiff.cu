@@ -1123,24 +1123,26 @@ static stream_wait32_fn get_stream_wait32()
     return fn;
 }
 
-static int halo_wait(adv_solver* s, int which, unsigned value)
+static int halo_wait(adv_solver* s, int which, unsigned value, cudaStream_t st = nullptr)
 {
+    if (!st) st = s->stream;
     unsigned* flag = (unsigned*)(s->arena + s->off_flags) + which;
     stream_wait32_fn w = get_stream_wait32();
     if (w) {
-        CUresult r = w((CUstream)s->stream, (CUdeviceptr)flag, value, 0 /* CU_STREAM_WAIT_VALUE_GEQ */);
+        CUresult r = w((CUstream)st, (CUdeviceptr)flag, value, 0 /* CU_STREAM_WAIT_VALUE_GEQ */);
         if (r == CUDA_SUCCESS) return ADV_OK;
     }
-    halo_wait_kernel<<<1, 1, 0, s->stream>>>(flag, value);
+    halo_wait_kernel<<<1, 1, 0, st>>>(flag, value);
     CUDA_TRY(cudaGetLastError());
     s->launches++;
     return ADV_OK;
 }
 
-static int halo_signal(adv_solver* s, int nbr, int which, unsigned value)
+static int halo_signal(adv_solver* s, int nbr, int which, unsigned value, cudaStream_t st = nullptr)
 {
+    if (!st) st = s->stream;
     unsigned* flag = (unsigned*)(s->peer_base[nbr] + s->off_flags) + which;
-    halo_signal_kernel<<<1, 1, 0, s->stream>>>(flag, value);
+    halo_signal_kernel<<<1, 1, 0, st>>>(flag, value);
     CUDA_TRY(cudaGetLastError());
     s->launches++;
     return ADV_OK;
@@ -1215,18 +1217,29 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
         if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, flo, flo, s->stream, po))) return rc;     // boundary windows only
         return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, kNoPeer);
     }
-    if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1))) return rc;
-    if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1))) return rc;
+    // Multi-launch schedule.  ADV_HALO_SIDE_STREAM=1 (A/B): the boundary launches, their flag waits and signals go to
+    // the side stream, forked from the main stream at the start of the stage and joined at the start of the next one,
+    // so that the interior launch can fill the SMs the short boundary CTAs leave idle.
+    const bool side = env_on("ADV_HALO_SIDE_STREAM");
+    cudaStream_t bs = side ? s->comm_stream : s->stream;
+    if (side) {
+        CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));        // join the previous stage's boundary work
+        CUDA_TRY(cudaEventRecord(s->ev_boundary, s->stream));           // fork: everything up to the previous interior launch
+        CUDA_TRY(cudaStreamWaitEvent(bs, s->ev_boundary, 0));
+    }
+    if (r > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, c - 1, bs))) return rc;
+    if (r < P - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, c - 1, bs))) return rc;
     if (r > 0) {            // my planes [3,6) are the left neighbour's ghost planes [nzs-3, nzs)
         PeerOut po = {s->peer_base[0] + s->off_buf[ob], (long long)(s->nzs - 2 * R) * plane};
-        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, R, 2 * R, s->stream, po))) return rc;
+        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, R, 2 * R, bs, po))) return rc;
     }
     if (r < P - 1) {        // my planes [nzs-6, nzs-3) are the right neighbour's ghost planes [0, 3)
         PeerOut po = {s->peer_base[1] + s->off_buf[ob], -(long long)(s->nzs - 2 * R) * plane};
-        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, s->nzs - 2 * R, s->nzs - R, s->stream, po))) return rc;
+        if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, s->nzs - 2 * R, s->nzs - R, bs, po))) return rc;
     }
-    if (r > 0 && (rc = halo_signal(s, 0, FLAG_FROM_RIGHT, c))) return rc;
-    if (r < P - 1 && (rc = halo_signal(s, 1, FLAG_FROM_LEFT, c))) return rc;
+    if (r > 0 && (rc = halo_signal(s, 0, FLAG_FROM_RIGHT, c, bs))) return rc;
+    if (r < P - 1 && (rc = halo_signal(s, 1, FLAG_FROM_LEFT, c, bs))) return rc;
+    if (side) CUDA_TRY(cudaEventRecord(s->ev_comm, bs));
     const int ilo = (r > 0) ? 2 * R : 0;
     const int ihi = (r < P - 1) ? s->nzs - 2 * R : s->nzs;
     return launch_stage_peer(s, stage, dt, in, uo, out, ilo, ihi, s->stream, kNoPeer);
@@ -1270,6 +1283,7 @@ static int halo_quiesce(adv_solver* s)
     if (!s->p2p) { CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0)); return ADV_OK; }
     int rc;
     if (s->stage_counter == 0) return ADV_OK;
+    CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));        // side-stream boundary work of the last stage, if any
     if (s->d.rank > 0 && (rc = halo_wait(s, FLAG_FROM_LEFT, s->stage_counter))) return rc;
     if (s->d.rank < s->d.nranks - 1 && (rc = halo_wait(s, FLAG_FROM_RIGHT, s->stage_counter))) return rc;
     return ADV_OK;
