@@ -1217,10 +1217,13 @@ static int do_stage_p2p(adv_solver* s, int stage, double dt, const void* in, con
         if ((rc = launch_stage_peer(s, stage, dt, in, uo, out, flo, flo, s->stream, po))) return rc;     // boundary windows only
         return launch_stage_peer(s, stage, dt, in, uo, out, flo, fhi, s->stream, kNoPeer);
     }
-    // Multi-launch schedule.  ADV_HALO_SIDE_STREAM=1 (A/B): the boundary launches, their flag waits and signals go to
-    // the side stream, forked from the main stream at the start of the stage and joined at the start of the next one,
-    // so that the interior launch can fill the SMs the short boundary CTAs leave idle.
-    const bool side = env_on("ADV_HALO_SIDE_STREAM");
+    // Multi-launch schedule.  For heat 3-D the boundary launches, their flag waits and signals go to the side stream,
+    // forked from the main stream at the start of the stage and joined at the start of the next one, so that the
+    // interior launch fills the SMs the short boundary CTAs leave idle: 4 B200s, 512^3 per GPU, 1.484 -> 1.426 ms per
+    // step (91.8 -> 95.6 % of the one-GPU rate), 1024^3 strong 3.06 -> 2.99 ms (profiles/r02_ab_side_4gpu.log).
+    // ADV_HALO_ONE_STREAM=1 keeps everything on one stream; ADV_HALO_SIDE_STREAM=1 turns the side stream on for the
+    // other multi-launch targets too (parity-tested, not timed).
+    const bool side = !env_on("ADV_HALO_ONE_STREAM") && (s->d.target == ADV_TARGET_HEAT3D_MGPU || env_on("ADV_HALO_SIDE_STREAM"));
     cudaStream_t bs = side ? s->comm_stream : s->stream;
     if (side) {
         CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_comm, 0));        // join the previous stage's boundary work
