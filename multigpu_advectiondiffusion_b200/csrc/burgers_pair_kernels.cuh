@@ -1,8 +1,9 @@
 // burgers3d_stage_pair: the fused 3-D Burgers stage (LF split + WENO5 JS/Z faces in x, y, z + divergence
-// [+ viscous term] + SSP-RK3 combine), third generation.  Same arithmetic as burgers3d_stage_ring
-// (weno_side6, pair formulation, (f+,f-) plane ring in shared memory); what changed is everything around the
-// arithmetic, because the kernel is bound by the issue port (an FP64 instruction holds it two cycles, anything
-// else one: DESIGN.md 3.2) and 31 % of the ring kernel's steady-state instructions were not FP64:
+// [+ viscous term] + SSP-RK3 combine), third generation.  Same formulas as burgers3d_stage_ring (pair formulation,
+// (f+,f-) plane ring in shared memory) with a leaner side routine (weno_core6, burgers_kernels.cuh: 40 FP64
+// instructions instead of weno_side6's 43); what changed most is everything around the arithmetic, because the kernel
+// is bound by the issue port (an FP64 instruction holds it two cycles, anything else one: DESIGN.md 3.2) and 31 % of
+// the ring kernel's steady-state instructions were not FP64:
 //
 //  * TMA staging.  Per plane ONE cp.async.bulk.tensor.3d box brings u of tile + halo (40 x 22 values, x halo
 //    4 so that the box origin falls on 16 bytes) into shared memory, issued by one elected thread a whole
@@ -20,9 +21,13 @@
 //  * No extra warp.  The 96 halves on the tile rim (64 in y, 32 in x) are three warp-rounds per plane, taken by
 //    three of the eight compute warps in rotation ((warp + plane) mod 8), so no scheduler carries a ninth warp
 //    and all four see the same load over time.
-//  * One body for every plane: window / ownership tests are block-uniform flags; only the finalisation of rim
-//    tiles (cells next to the domain faces, the i = 2 / j = 2 pseudo-updates, the j = 2 scratch row) is
-//    compiled separately (RIM), chosen per CTA.
+//  * Steady state: planes for which every window / ownership / staging test is true run a body compiled without
+//    them (STEADY), unrolled by two so that the buffers that alternate from plane to plane have compile-time indices;
+//    the x-rim halves are computed one plane ahead, so the finalisation has no special lanes.  The finalisation of rim
+//    tiles (cells next to the domain faces, the i = 2 / j = 2 pseudo-updates, the j = 2 scratch row) is compiled
+//    separately (RIM), chosen per CTA.
+//  * Multi-rank slabs: the launch's first z chunks can be the boundary windows of a fused halo exchange (SlabSched,
+//    common.cuh); a dynamic-CFL run reads dt / done from device memory and (TRACK) folds max|u| into stage 3.
 // Reference: Compute_dF/dG/dH + Reconstruct1d + Compute_RK, MultiGPU/Burgers3d_Baseline/Kernels.cu:112-486;
 // WENO5Zreconstruction + Compute_Laplace_Async + Compute_RK, SingleGPU/Burgers3d_WENO5/kernels.cu:142-530.
 #pragma once
